@@ -1,0 +1,549 @@
+// fs2_cabi.cu — libfs2cuda.so: the C ABI of include/fs2_cabi.h over the sm_100a kernels.
+//
+// Host side only does plumbing: validation, uploads, the per-frame camera basis
+// (reference source/engine.cpp:170-197, evaluated with the host libm exactly like the
+// reference does), launches, read-back.  There is no CPU tracing path in this library:
+// without a CUDA device every compute entry point fails with FS_E_CUDA.
+//
+// Build: nvcc -gencode arch=compute_100a,code=sm_100a -O3 -lineinfo -fmad=false
+//        -Xcompiler -fPIC,-ffp-contract=off -shared   (see ../build.py)
+#include <math.h>
+#include <stdarg.h>
+#include <stdio.h>
+#include <string.h>
+
+#include <string>
+#include <vector>
+
+#include "fs2_kernels.cuh"
+
+using namespace fs2;
+
+namespace {
+
+thread_local char g_error[512] = "";
+
+struct DeviceBuf {
+  void* p = nullptr;
+  size_t bytes = 0;
+};
+
+}  // namespace
+
+struct fs_ctx {
+  int device = 0;
+  cudaStream_t stream = nullptr;
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  char error[512] = "";
+  // scene
+  bool have_scene = false;
+  DeviceBuf nodes, scene_refs, tri_plane, tri_aux, faces, objects, materials, textures, texels,
+      lut;
+  DScene ds;
+  uint32_t n_nodes = 0, n_tris = 0, n_faces = 0, n_materials = 0;
+  // film
+  int width = 0, height = 0;
+  DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch;
+  // stats
+  unsigned long long* d_stats = nullptr;
+  uint64_t launches = 0;
+  float last_trace_ms = 0.f;
+  bool stats_build = false;
+};
+
+namespace {
+
+int fail(fs_ctx* ctx, int code, const char* fmt, ...) {
+  va_list ap;
+  va_start(ap, fmt);
+  vsnprintf(g_error, sizeof g_error, fmt, ap);
+  va_end(ap);
+  if (ctx) memcpy(ctx->error, g_error, sizeof g_error);
+  return code;
+}
+
+#define CUDA_TRY(ctx, call)                                                               \
+  do {                                                                                    \
+    cudaError_t e_ = (call);                                                              \
+    if (e_ != cudaSuccess)                                                                \
+      return fail(ctx, FS_E_CUDA, "%s: %s (%s:%d)", #call, cudaGetErrorString(e_), __FILE__, \
+                  __LINE__);                                                              \
+  } while (0)
+
+int dev_alloc(fs_ctx* ctx, DeviceBuf* b, size_t bytes) {
+  if (b->p && b->bytes >= bytes && bytes) return FS_OK;
+  if (b->p) {
+    cudaFree(b->p);
+    b->p = nullptr;
+    b->bytes = 0;
+  }
+  if (!bytes) bytes = 16;  // keep pointers valid for empty arrays
+  CUDA_TRY(ctx, cudaMalloc(&b->p, bytes));
+  b->bytes = bytes;
+  return FS_OK;
+}
+
+int dev_upload(fs_ctx* ctx, DeviceBuf* b, const void* src, size_t bytes) {
+  int rc = dev_alloc(ctx, b, bytes);
+  if (rc) return rc;
+  if (bytes) CUDA_TRY(ctx, cudaMemcpyAsync(b->p, src, bytes, cudaMemcpyHostToDevice, ctx->stream));
+  return FS_OK;
+}
+
+void dev_free(DeviceBuf* b) {
+  if (b->p) cudaFree(b->p);
+  b->p = nullptr;
+  b->bytes = 0;
+}
+
+// ---- host restatement of the reference's approximate vector helpers, used only for
+// the per-frame camera basis (reference source/math/scalar.h:233-245, vector3.h:166-187)
+struct H3 {
+  float x, y, z;
+};
+float h_inv_sqrt(float f) {
+  float half = 0.5f * f;
+  int32_t i;
+  memcpy(&i, &f, 4);
+  i = 0x5f3759df - (i >> 1);
+  memcpy(&f, &i, 4);
+  return f * (1.5f - half * f * f);
+}
+H3 h_normalize(H3 a) {
+  float l = 1.0f / h_inv_sqrt(a.x * a.x + a.y * a.y + a.z * a.z);
+  if (l == 0.0f) l = 1.0f;
+  return H3{a.x / l, a.y / l, a.z / l};
+}
+H3 h_cross(H3 a, H3 b) {
+  return H3{(a.y * b.z) - (a.z * b.y), (a.z * b.x) - (a.x * b.z), (a.x * b.y) - (a.y * b.x)};
+}
+
+// reference source/engine.cpp:170-197 (and :300-313 for TraceRange)
+CamBasis camera_basis(const fs_camera* cam, int w, int h) {
+  CamBasis b;
+  memset(&b, 0, sizeof b);
+  float width = (float)w, height = (float)h;
+  float aspect = width / height;
+  float fovy = cam->fov_y * FS2_PI / 180.0;
+  float fovx = 2.0 * atan(tan(fovy * 0.5) * aspect);
+  H3 origin{cam->origin[0], cam->origin[1], cam->origin[2]};
+  H3 target{cam->target[0], cam->target[1], cam->target[2]};
+  H3 fwd = h_normalize(H3{target.x - origin.x, target.y - origin.y, target.z - origin.z});
+  H3 right = h_normalize(h_cross(H3{0.f, 1.f, 0.f}, fwd));
+  H3 up = h_normalize(h_cross(fwd, right));
+  b.half_h = tanf(fovy * 0.5f) * cam->z_far;
+  b.half_w = tanf(fovx * 0.5f) * cam->z_far;
+  H3 proj{origin.x + fwd.x * cam->z_far, origin.y + fwd.y * cam->z_far,
+          origin.z + fwd.z * cam->z_far};
+  // focal plane: calculate_plane(-forward, origin + forward * focal_depth) (engine.cpp:195-197)
+  H3 n{fwd.x * -1.0f, fwd.y * -1.0f, fwd.z * -1.0f};
+  H3 fp{origin.x + fwd.x * cam->focal_depth, origin.y + fwd.y * cam->focal_depth,
+        origin.z + fwd.z * cam->focal_depth};
+  float d = -(n.x * fp.x + n.y * fp.y + n.z * fp.z);
+  float* dst[5] = {b.origin, b.right, b.up, b.forward, b.proj_origin};
+  H3 src[5] = {origin, right, up, fwd, proj};
+  for (int k = 0; k < 5; k++) {
+    dst[k][0] = src[k].x;
+    dst[k][1] = src[k].y;
+    dst[k][2] = src[k].z;
+  }
+  b.focal_plane[0] = n.x;
+  b.focal_plane[1] = n.y;
+  b.focal_plane[2] = n.z;
+  b.focal_plane[3] = d;
+  b.wm1 = width - 1;
+  b.hm1 = height - 1;
+  b.aperture = cam->aperture_size;
+  b.z_far = cam->z_far;
+  b.fast_render = cam->fast_render_enabled;
+  return b;
+}
+
+int validate_scene(fs_ctx* ctx, const fs_scene_desc* s) {
+  if (s->abi_version != FS2_ABI_VERSION)
+    return fail(ctx, FS_E_INVALID, "scene abi_version %u != %d", s->abi_version, FS2_ABI_VERSION);
+  if (s->n_materials == 0 || s->sky_material >= s->n_materials)
+    return fail(ctx, FS_E_INVALID, "sky_material %u out of range (%u materials)", s->sky_material,
+                s->n_materials);
+  if (s->n_lut == 0 || !s->lut) return fail(ctx, FS_E_INVALID, "normal LUT missing");
+  if ((s->n_nodes && !s->nodes) || (s->n_tris && (!s->tri_plane || !s->tri_aux)) ||
+      (s->n_faces && !s->faces) || (s->n_objects && !s->objects) || !s->materials ||
+      (s->n_textures && (!s->textures || !s->texels)) || (s->n_scene_refs && !s->scene_refs))
+    return fail(ctx, FS_E_INVALID, "null array with non-zero count");
+  if (s->scene_root >= 0 && (uint32_t)s->scene_root >= s->n_nodes)
+    return fail(ctx, FS_E_INVALID, "scene_root %d out of range", s->scene_root);
+  for (uint32_t i = 0; i < s->n_nodes; i++) {
+    const fs_node& n = s->nodes[i];
+    if (n.count == FS_NODE_INTERNAL) {
+      if ((uint64_t)n.first + 8 > s->n_nodes)
+        return fail(ctx, FS_E_INVALID, "node %u: children out of range", i);
+    }
+  }
+  for (uint32_t i = 0; i < s->n_objects; i++) {
+    const fs_object& o = s->objects[i];
+    if (o.type > FS_OBJ_MESH) return fail(ctx, FS_E_INVALID, "object %u: bad type %u", i, o.type);
+    if (o.material >= s->n_materials)
+      return fail(ctx, FS_E_INVALID, "object %u: material %u out of range", i, o.material);
+    if (o.type == FS_OBJ_MESH && o.u[0] != 0xFFFFFFFFu) {
+      if (o.u[0] >= s->n_nodes) return fail(ctx, FS_E_INVALID, "object %u: mesh root out of range", i);
+      if ((uint64_t)o.u[1] + o.u[3] > s->n_faces)
+        return fail(ctx, FS_E_INVALID, "object %u: face range out of bounds", i);
+    }
+  }
+  for (uint32_t i = 0; i < s->n_scene_refs; i++)
+    if (s->scene_refs[i] >= s->n_objects)
+      return fail(ctx, FS_E_INVALID, "scene ref %u out of range", i);
+  for (uint32_t i = 0; i < s->n_tris; i++)
+    if ((s->tri_aux[i].face & 0x3FFFFFFFu) >= s->n_faces)
+      return fail(ctx, FS_E_INVALID, "triangle %u: face index out of range", i);
+  for (uint32_t i = 0; i < s->n_materials; i++) {
+    const fs_material& m = s->materials[i];
+    if (m.type > FS_MAT_FOG) return fail(ctx, FS_E_INVALID, "material %u: bad type", i);
+    if (m.texture >= (int32_t)s->n_textures)
+      return fail(ctx, FS_E_INVALID, "material %u: texture out of range", i);
+  }
+  for (uint32_t i = 0; i < s->n_textures; i++) {
+    const fs_texture& t = s->textures[i];
+    if (!t.width || !t.height || t.offset + (uint64_t)t.width * t.height * 3 > s->n_texels)
+      return fail(ctx, FS_E_INVALID, "texture %u: out of range", i);
+  }
+  return FS_OK;
+}
+
+int set_device(fs_ctx* ctx) {
+  CUDA_TRY(ctx, cudaSetDevice(ctx->device));
+  return FS_OK;
+}
+
+dim3 pixel_grid(int w, int h) { return dim3((w + 15) / 16, (h + 7) / 8); }
+
+}  // namespace
+
+extern "C" {
+
+int fs_abi_version(void) { return FS2_ABI_VERSION; }
+
+const char* fs_last_error(const fs_ctx* ctx) { return ctx ? ctx->error : g_error; }
+
+int fs_create(fs_ctx** out, int device, int flags) {
+  if (!out) return fail(nullptr, FS_E_INVALID, "fs_create: null out pointer");
+  *out = nullptr;
+  int n = 0;
+  cudaError_t e = cudaGetDeviceCount(&n);
+  if (e != cudaSuccess || n == 0)
+    return fail(nullptr, FS_E_CUDA, "no CUDA device: %s", cudaGetErrorString(e));
+  if (device < 0 || device >= n)
+    return fail(nullptr, FS_E_INVALID, "device %d out of range (%d devices)", device, n);
+  fs_ctx* ctx = new (std::nothrow) fs_ctx();
+  if (!ctx) return fail(nullptr, FS_E_NOMEM, "out of host memory");
+  ctx->device = device;
+  ctx->stats_build = (flags & 1) != 0;
+  int rc = set_device(ctx);
+  if (rc == FS_OK) {
+    cudaError_t e1 = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->ev0);
+    if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->ev1);
+    if (e1 == cudaSuccess) e1 = cudaMalloc(&ctx->d_stats, ST_COUNT * sizeof(unsigned long long));
+    if (e1 == cudaSuccess)
+      e1 = cudaMemset(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long));
+    if (e1 != cudaSuccess) rc = fail(nullptr, FS_E_CUDA, "fs_create: %s", cudaGetErrorString(e1));
+  }
+  if (rc != FS_OK) {
+    delete ctx;
+    return rc;
+  }
+  *out = ctx;
+  return FS_OK;
+}
+
+int fs_destroy(fs_ctx* ctx) {
+  if (!ctx) return FS_OK;
+  cudaSetDevice(ctx->device);
+  cudaStreamSynchronize(ctx->stream);
+  DeviceBuf* all[] = {&ctx->nodes, &ctx->scene_refs, &ctx->tri_plane, &ctx->tri_aux, &ctx->faces,
+                      &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
+                      &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
+                      &ctx->scratch};
+  for (DeviceBuf* b : all) dev_free(b);
+  if (ctx->d_stats) cudaFree(ctx->d_stats);
+  if (ctx->ev0) cudaEventDestroy(ctx->ev0);
+  if (ctx->ev1) cudaEventDestroy(ctx->ev1);
+  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  delete ctx;
+  return FS_OK;
+}
+
+int fs_scene_upload(fs_ctx* ctx, const fs_scene_desc* s) {
+  if (!ctx || !s) return fail(ctx, FS_E_INVALID, "fs_scene_upload: null argument");
+  int rc = validate_scene(ctx, s);
+  if (rc) return rc;
+  if ((rc = set_device(ctx))) return rc;
+  ctx->have_scene = false;
+  // LUT repacked to 16 bytes per entry so one ld.global.v4 fetches a normal
+  std::vector<float> lut4((size_t)s->n_lut * 4);
+  for (uint32_t i = 0; i < s->n_lut; i++) {
+    lut4[4 * (size_t)i + 0] = s->lut[3 * (size_t)i + 0];
+    lut4[4 * (size_t)i + 1] = s->lut[3 * (size_t)i + 1];
+    lut4[4 * (size_t)i + 2] = s->lut[3 * (size_t)i + 2];
+    lut4[4 * (size_t)i + 3] = 0.f;
+  }
+  if ((rc = dev_upload(ctx, &ctx->nodes, s->nodes, (size_t)s->n_nodes * sizeof(fs_node)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->scene_refs, s->scene_refs, (size_t)s->n_scene_refs * 4))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->tri_plane, s->tri_plane, (size_t)s->n_tris * 16))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->tri_aux, s->tri_aux, (size_t)s->n_tris * sizeof(fs_tri_aux)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->faces, s->faces, (size_t)s->n_faces * sizeof(fs_face_attr)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->objects, s->objects, (size_t)s->n_objects * sizeof(fs_object)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->materials, s->materials, (size_t)s->n_materials * sizeof(fs_material)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->textures, s->textures, (size_t)s->n_textures * sizeof(fs_texture)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->texels, s->texels, (size_t)s->n_texels * 4))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lut, lut4.data(), lut4.size() * 4))) return rc;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  DScene& d = ctx->ds;
+  d.nodes = (const float4*)ctx->nodes.p;
+  d.scene_refs = (const uint32_t*)ctx->scene_refs.p;
+  d.tri_plane = (const float4*)ctx->tri_plane.p;
+  d.tri_aux = (const float4*)ctx->tri_aux.p;
+  d.faces = (const float4*)ctx->faces.p;
+  d.objects = (const float4*)ctx->objects.p;
+  d.materials = (const float4*)ctx->materials.p;
+  d.textures = (const fs_texture*)ctx->textures.p;
+  d.texels = (const float*)ctx->texels.p;
+  d.lut = (const float4*)ctx->lut.p;
+  d.n_objects = s->n_objects;
+  d.n_lut = s->n_lut;
+  d.sky_material = s->sky_material;
+  d.scene_root = s->scene_root;
+  ctx->n_nodes = s->n_nodes;
+  ctx->n_tris = s->n_tris;
+  ctx->n_faces = s->n_faces;
+  ctx->n_materials = s->n_materials;
+  ctx->have_scene = true;
+  return FS_OK;
+}
+
+int fs_film_resize(fs_ctx* ctx, int width, int height) {
+  if (!ctx || width <= 0 || height <= 0 || (int64_t)width * height > (1ll << 30))
+    return fail(ctx, FS_E_INVALID, "fs_film_resize: bad size %dx%d", width, height);
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  size_t n = (size_t)width * height;
+  if ((rc = dev_alloc(ctx, &ctx->sum, n * 16))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->aux, n * 16))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->mat_id, n * 4))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->mean, n * 12))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->count, n * 4))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->rgb8, n * 3))) return rc;
+  ctx->width = width;
+  ctx->height = height;
+  return fs_film_reset(ctx);
+}
+
+int fs_film_reset(fs_ctx* ctx) {
+  if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_reset before fs_film_resize");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  size_t n = (size_t)ctx->width * ctx->height;
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->sum.p, 0, n * 16, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->aux.p, 0, n * 16, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->mat_id.p, 0, n * 4, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->mean.p, 0, n * 12, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->count.p, 0, n * 4, ctx->stream));
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->rgb8.p, 0, n * 3, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_first_hit(fs_ctx* ctx, const fs_camera* cam, int width, int height, float* t,
+                 uint32_t* object, uint32_t* face, uint32_t* mat_id, float* range) {
+  if (!ctx || !cam || width <= 1 || height <= 1)
+    return fail(ctx, FS_E_INVALID, "fs_first_hit: bad argument");
+  if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_first_hit before fs_scene_upload");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  size_t n = (size_t)width * height;
+  if ((rc = dev_alloc(ctx, &ctx->scratch, n * 20))) return rc;
+  char* base = (char*)ctx->scratch.p;
+  float* d_t = (float*)base;
+  uint32_t* d_obj = (uint32_t*)(base + n * 4);
+  uint32_t* d_face = (uint32_t*)(base + n * 8);
+  uint32_t* d_mat = (uint32_t*)(base + n * 12);
+  float* d_range = (float*)(base + n * 16);
+  CamBasis cb = camera_basis(cam, width, height);
+  k_first_hit<<<pixel_grid(width, height), 128, 0, ctx->stream>>>(ctx->ds, cb, width, height, d_t,
+                                                                  d_obj, d_face, d_mat, d_range,
+                                                                  ctx->d_stats);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  if (t) CUDA_TRY(ctx, cudaMemcpyAsync(t, d_t, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (object) CUDA_TRY(ctx, cudaMemcpyAsync(object, d_obj, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (face) CUDA_TRY(ctx, cudaMemcpyAsync(face, d_face, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (mat_id) CUDA_TRY(ctx, cudaMemcpyAsync(mat_id, d_mat, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (range) CUDA_TRY(ctx, cudaMemcpyAsync(range, d_range, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_trace_range(fs_ctx* ctx, const fs_camera* cam, int width, int height, float x, float y,
+                   float* range) {
+  // TraceRange(viewer, scene, frame, x, y): fractional pixel coordinates are expressed as a
+  // 2x2 query whose pixel (0,0) carries the requested offset: (x/(W-1))*2-1 only depends on
+  // x and W, so a single-pixel launch with the real width/height is used instead.
+  if (!ctx || !cam || !range || width <= 1 || height <= 1)
+    return fail(ctx, FS_E_INVALID, "fs_trace_range: bad argument");
+  if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_trace_range before fs_scene_upload");
+  if (!(x >= 0.0f && y >= 0.0f && x <= (float)(width - 1) && y <= (float)(height - 1)))
+    return fail(ctx, FS_E_INVALID, "fs_trace_range: (%g,%g) outside the image", x, y);
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->scratch, 64))) return rc;
+  CamBasis cb = camera_basis(cam, width, height);
+  // shift the projection origin so that pixel (0,0) of a 1x1 launch is (x, y)
+  float xd = (float)((double)cb.half_w * ((double)(x / cb.wm1) * 2.0 - 1.0));
+  float yd = (float)((double)cb.half_h * ((double)(y / cb.hm1) * 2.0 - 1.0));
+  CamBasis one = cb;
+  // pixel (0,0) maps to xd' = half_w * (0*2 - 1) = -half_w; choose half extents so that
+  // -half_w' == xd, -half_h' == yd (exact: negation only).
+  one.half_w = -xd;
+  one.half_h = -yd;
+  float* d_range = (float*)ctx->scratch.p;
+  k_first_hit<<<dim3(1, 1), 128, 0, ctx->stream>>>(ctx->ds, one, 1, 1, nullptr, nullptr, nullptr,
+                                                  nullptr, d_range, ctx->d_stats);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaMemcpyAsync(range, d_range, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_film_resolve(fs_ctx* ctx) {
+  if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_resolve before fs_film_resize");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  int n = ctx->width * ctx->height;
+  k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>((const float4*)ctx->sum.p, n,
+                                                      (float*)ctx->mean.p, (uint32_t*)ctx->count.p,
+                                                      (uint8_t*)ctx->rgb8.p);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t n_samples,
+             uint32_t sample_stride, uint64_t seed, int flags) {
+  if (!ctx || !cam) return fail(ctx, FS_E_INVALID, "fs_trace: null argument");
+  if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_trace before fs_scene_upload");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_trace before fs_film_resize");
+  if (ctx->width < 2 || ctx->height < 2)
+    return fail(ctx, FS_E_INVALID, "fs_trace: film must be at least 2x2");
+  if (sample_stride == 0) sample_stride = 1;
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  CamBasis cb = camera_basis(cam, ctx->width, ctx->height);
+  Film film{(float4*)ctx->sum.p, (float4*)ctx->aux.p, (uint32_t*)ctx->mat_id.p, ctx->width,
+            ctx->height};
+  TraceParams tp{first_sample, n_samples, sample_stride, seed, flags};
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  if (n_samples) {
+    dim3 grid = pixel_grid(ctx->width, ctx->height);
+    if (ctx->stats_build)
+      k_trace_mega<true><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
+    else
+      k_trace_mega<false><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+  }
+  if (!(flags & FS_TRACE_NO_RESOLVE)) {
+    int n = ctx->width * ctx->height;
+    k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(
+        (const float4*)ctx->sum.p, n, (float*)ctx->mean.p, (uint32_t*)ctx->count.p,
+        (uint8_t*)ctx->rgb8.p);
+    ctx->launches++;
+    CUDA_TRY(ctx, cudaGetLastError());
+  }
+  CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->last_trace_ms, ctx->ev0, ctx->ev1));
+  return FS_OK;
+}
+
+int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8, float* normal,
+                 float* depth, uint64_t* mat_id) {
+  if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_read before fs_film_resize");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  size_t n = (size_t)ctx->width * ctx->height;
+  if (mean_rgb) CUDA_TRY(ctx, cudaMemcpyAsync(mean_rgb, ctx->mean.p, n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+  if (count) CUDA_TRY(ctx, cudaMemcpyAsync(count, ctx->count.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (rgb8) CUDA_TRY(ctx, cudaMemcpyAsync(rgb8, ctx->rgb8.p, n * 3, cudaMemcpyDeviceToHost, ctx->stream));
+  std::vector<float> aux;
+  std::vector<uint32_t> ids;
+  if (normal || depth) {
+    aux.resize(n * 4);
+    CUDA_TRY(ctx, cudaMemcpyAsync(aux.data(), ctx->aux.p, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  if (mat_id) {
+    ids.resize(n);
+    CUDA_TRY(ctx, cudaMemcpyAsync(ids.data(), ctx->mat_id.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  }
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  for (size_t i = 0; i < n && (normal || depth); i++) {
+    if (normal) {
+      normal[3 * i] = aux[4 * i];
+      normal[3 * i + 1] = aux[4 * i + 1];
+      normal[3 * i + 2] = aux[4 * i + 2];
+    }
+    if (depth) depth[i] = aux[4 * i + 3];
+  }
+  for (size_t i = 0; i < n && mat_id; i++) mat_id[i] = ids[i];
+  return FS_OK;
+}
+
+int fs_film_device(fs_ctx* ctx, void** sum_rgba, size_t* n_floats) {
+  if (!ctx || !sum_rgba || !n_floats) return fail(ctx, FS_E_INVALID, "null argument");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_device before fs_film_resize");
+  *sum_rgba = ctx->sum.p;
+  *n_floats = (size_t)ctx->width * ctx->height * 4;
+  return FS_OK;
+}
+
+int fs_get_stats(fs_ctx* ctx, fs_stats* out) {
+  if (!ctx || !out) return fail(ctx, FS_E_INVALID, "null argument");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  unsigned long long h[ST_COUNT];
+  CUDA_TRY(ctx, cudaMemcpyAsync(h, ctx->d_stats, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  memset(out, 0, sizeof *out);
+  out->n_paths = h[ST_PATHS];
+  out->n_segments = h[ST_SEGMENTS];
+  out->n_node = h[ST_NODE];
+  out->n_tri = h[ST_TRI];
+  out->n_bary = h[ST_BARY];
+  out->n_prim = h[ST_PRIM];
+  out->n_shade = h[ST_SHADE];
+  out->launches = ctx->launches;
+  out->last_trace_ms = ctx->last_trace_ms;
+  return FS_OK;
+}
+
+int fs_reset_stats(fs_ctx* ctx) {
+  if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  ctx->launches = 0;
+  return FS_OK;
+}
+
+int fs_get_stream(fs_ctx* ctx, void** stream) {
+  if (!ctx || !stream) return fail(ctx, FS_E_INVALID, "null argument");
+  *stream = (void*)ctx->stream;
+  return FS_OK;
+}
+
+}  // extern "C"

@@ -1,0 +1,174 @@
+"""ctypes plumbing over libfs2cuda.so (include/fs2_cabi.h).  No tracing arithmetic here and
+no fallback: if the CUDA library is missing or no device is present, calls raise."""
+import ctypes as C
+import os
+
+import numpy as np
+
+from . import abi, build
+
+_SYMBOLS = {
+    "fs_abi_version": (C.c_int, []),
+    "fs_last_error": (C.c_char_p, [C.c_void_p]),
+    "fs_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int]),
+    "fs_destroy": (C.c_int, [C.c_void_p]),
+    "fs_scene_upload": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_scene_desc)]),
+    "fs_film_resize": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "fs_film_reset": (C.c_int, [C.c_void_p]),
+    "fs_first_hit": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_int, C.c_int,
+                               C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
+    "fs_trace_range": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_int, C.c_int,
+                                 C.c_float, C.c_float, C.POINTER(C.c_float)]),
+    "fs_trace": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_uint32, C.c_uint32,
+                           C.c_uint32, C.c_uint64, C.c_int]),
+    "fs_film_read": (C.c_int, [C.c_void_p] + [C.c_void_p] * 6),
+    "fs_film_device": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_size_t)]),
+    "fs_film_resolve": (C.c_int, [C.c_void_p]),
+    "fs_get_stats": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_stats)]),
+    "fs_reset_stats": (C.c_int, [C.c_void_p]),
+    "fs_get_stream": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+}
+
+_lib = None
+
+
+class Fs2Error(RuntimeError):
+    def __init__(self, code, message):
+        super().__init__("fs2 error %d: %s" % (code, message))
+        self.code = code
+
+
+def load_library(path=None):
+    """Loads libfs2cuda.so (building it in-tree if the sources are newer) and declares
+    every entry point of include/fs2_cabi.h.  Raises if the library cannot be loaded."""
+    global _lib
+    if _lib is not None and path is None:
+        return _lib
+    if path is None:
+        path = build.CUDA_LIB
+        if not os.path.exists(path):
+            build.build_cuda()
+    lib = C.CDLL(path)
+    for name, (res, args) in _SYMBOLS.items():
+        fn = getattr(lib, name)  # AttributeError if the symbol is missing
+        fn.restype = res
+        fn.argtypes = args
+    _lib = lib
+    return lib
+
+
+def exported_symbols():
+    return sorted(_SYMBOLS)
+
+
+def _ptr(a):
+    return a.ctypes.data_as(C.c_void_p) if a is not None else None
+
+
+class Context:
+    """One fs_ctx: a scene resident on one GPU plus its film."""
+
+    def __init__(self, device=0, stats=False):
+        self.lib = load_library()
+        self.handle = C.c_void_p()
+        rc = self.lib.fs_create(C.byref(self.handle), device, 1 if stats else 0)
+        if rc != 0:
+            raise Fs2Error(rc, (self.lib.fs_last_error(None) or b"").decode())
+        self.device = device
+        self.width = self.height = 0
+
+    def _check(self, rc):
+        if rc != 0:
+            raise Fs2Error(rc, (self.lib.fs_last_error(self.handle) or b"").decode())
+
+    def close(self):
+        if self.handle:
+            self.lib.fs_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    # ---- scene / film ----------------------------------------------------------
+    def upload(self, scene):
+        d = scene.desc() if isinstance(scene, abi.FlatScene) else scene
+        self._check(self.lib.fs_scene_upload(self.handle, C.byref(d)))
+
+    def resize(self, width, height):
+        self._check(self.lib.fs_film_resize(self.handle, width, height))
+        self.width, self.height = width, height
+
+    def reset(self):
+        self._check(self.lib.fs_film_reset(self.handle))
+
+    # ---- queries ---------------------------------------------------------------
+    def first_hit(self, cam, width, height):
+        n = width * height
+        out = {"t": np.empty(n, np.float32), "object": np.empty(n, np.uint32),
+               "face": np.empty(n, np.uint32), "mat_id": np.empty(n, np.uint32),
+               "range": np.empty(n, np.float32)}
+        self._check(self.lib.fs_first_hit(self.handle, C.byref(cam), width, height,
+                                          _ptr(out["t"]), _ptr(out["object"]), _ptr(out["face"]),
+                                          _ptr(out["mat_id"]), _ptr(out["range"])))
+        return out
+
+    def trace_range(self, cam, width, height, x, y):
+        r = C.c_float()
+        self._check(self.lib.fs_trace_range(self.handle, C.byref(cam), width, height, x, y,
+                                            C.byref(r)))
+        return r.value
+
+    def trace(self, cam, n_samples, first_sample=0, stride=1, seed=1, flags=0):
+        self._check(self.lib.fs_trace(self.handle, C.byref(cam), first_sample, n_samples, stride,
+                                      seed, flags))
+
+    def resolve(self):
+        self._check(self.lib.fs_film_resolve(self.handle))
+
+    def read_film(self, mean=True, count=True, rgb8=True, aux=False, out=None):
+        n = self.width * self.height
+        film = out if out is not None else {}
+        if mean and "mean" not in film:
+            film["mean"] = np.empty((n, 3), np.float32)
+        if count and "count" not in film:
+            film["count"] = np.empty(n, np.uint32)
+        if rgb8 and "rgb8" not in film:
+            film["rgb8"] = np.empty((n, 3), np.uint8)
+        if aux:
+            film.setdefault("normal", np.empty((n, 3), np.float32))
+            film.setdefault("depth", np.empty(n, np.float32))
+            film.setdefault("mat_id", np.empty(n, np.uint64))
+        self._check(self.lib.fs_film_read(self.handle, _ptr(film.get("mean")),
+                                          _ptr(film.get("count")), _ptr(film.get("rgb8")),
+                                          _ptr(film.get("normal")), _ptr(film.get("depth")),
+                                          _ptr(film.get("mat_id"))))
+        return film
+
+    def film_device(self):
+        """(device pointer, float count) of the rgb-sum/count film for an external reduce."""
+        p = C.c_void_p()
+        n = C.c_size_t()
+        self._check(self.lib.fs_film_device(self.handle, C.byref(p), C.byref(n)))
+        return p.value, n.value
+
+    def stream(self):
+        p = C.c_void_p()
+        self._check(self.lib.fs_get_stream(self.handle, C.byref(p)))
+        return p.value or 0
+
+    def stats(self):
+        s = abi.fs_stats()
+        self._check(self.lib.fs_get_stats(self.handle, C.byref(s)))
+        return {k: getattr(s, k) for k, _ in abi.fs_stats._fields_ if k != "pad"}
+
+    def reset_stats(self):
+        self._check(self.lib.fs_reset_stats(self.handle))

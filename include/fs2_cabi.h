@@ -64,6 +64,7 @@ extern "C" {
 
 #define FS_NODE_INTERNAL 0xFFFFFFFFu /* fs_node.count value marking an internal node */
 #define FS_NO_HIT_PARAM 2.0f         /* reference source/math/trace.cpp:18-21 */
+#define FS_CREATE_STATS 1            /* fs_create flag: count node/triangle/primitive tests */
 #define FS_LUT_SIZE 32768            /* reference source/material.cpp:17 */
 
 /*

@@ -439,6 +439,44 @@ static int render(Scene* scene, const Camera& cam, uint32_t W, uint32_t H, uint3
   return 0;
 }
 
+// ---------------------------------------------------------------- built-in API scene
+// Objects and materials the .scene grammar cannot express: PlanarObject,
+// DiscObject, FogMaterial, GlowMaterial, textured Metal — built through the reference's
+// own C++ API (source/scene.h:94-133, source/material.h:88-328).
+static void build_api_scene(Scene* scene, const char* texture_path) {
+  auto sky = std::make_shared<LightMaterial>(vector3(0.35f, 0.45f, 0.6f));
+  scene->SetSkyMaterial(sky);
+  auto floor_mat = std::make_shared<DiffuseMaterial>(vector3(0.7f, 0.7f, 0.65f));
+  if (texture_path && texture_path[0]) floor_mat->LoadDiffuseTexture(texture_path, 0.05f);
+  auto fog = std::make_shared<FogMaterial>(vector3(0.8f, 0.85f, 0.9f), 0.6f);
+  auto glow = std::make_shared<GlowMaterial>(vector3(0.3f, 0.2f, 0.8f), vector3(0.4f, 0.1f, 0.9f), 0.7f);
+  auto metal = std::make_shared<MetalMaterial>(vector3(0.9f, 0.6f, 0.3f), 0.97f);
+  auto ceramic = std::make_shared<CeramicMaterial>(vector3(0.8f, 0.3f, 0.2f), 0.4f);
+  auto lamp = std::make_shared<LightMaterial>(vector3(14.0f, 13.0f, 11.0f));
+  auto glass = std::make_shared<GlassMaterial>(vector3(0.95f, 0.97f, 1.0f), 1.0f, 0.05f, 0.35f);
+  auto diffuse = std::make_shared<DiffuseMaterial>(vector3(0.2f, 0.6f, 0.3f));
+
+  const char* mask_env = getenv("FS2_API_MASK");  // debugging aid: bit k keeps object k
+  unsigned mask = mask_env ? (unsigned)strtoul(mask_env, nullptr, 0) : 0xFFu;
+  if (mask & 1) scene->AddPlanarObject(calculate_plane(vector3(0.01f, 1.0f, 0.02f).normalize(), vector3(0, 0, 0)))
+      ->SetMaterial(floor_mat);
+  if (mask & 2) scene->AddDiscObject(vector3(-14.0f, 6.0f, 10.0f), vector3(0.3f, 0.2f, -1.0f).normalize(), 6.0f)
+      ->SetMaterial(metal);
+  if (mask & 4) {
+    CuboidObject* fog_box = scene->AddCuboidObject(vector3(4.0f, 7.0f, -8.0f), 14.0f, 12.0f, 10.0f);
+    fog_box->Rotate(vector3(0, 1, 0), 0.35f);
+    fog_box->SetMaterial(fog);
+  }
+  if (mask & 8) scene->AddSphericalObject(vector3(4.0f, 6.0f, -8.0f), 3.0f)->SetMaterial(glow);
+  if (mask & 16) scene->AddSphericalObject(vector3(-6.0f, 4.0f, -12.0f), 4.0f)->SetMaterial(ceramic);
+  if (mask & 32) scene->AddSphericalObject(vector3(14.0f, 5.0f, 2.0f), 5.0f)->SetMaterial(glass);
+  if (mask & 64) scene->AddSphericalObject(vector3(-2.0f, 32.0f, -6.0f), 5.0f)->SetMaterial(lamp);
+  if (mask & 128) scene->AddQuadObject(vector3(-20.0f, 14.0f, 16.0f), vector3(12.0f, 0.0f, 3.0f),
+                       vector3(0.0f, -10.0f, 0.5f))
+      ->SetMaterial(diffuse);
+  scene->Optimize();
+}
+
 // ---------------------------------------------------------------- main
 static void usage() {
   fprintf(stderr,
@@ -482,7 +520,12 @@ int main(int argc, char** argv) {
   // LoadScene (material ids), then InitializeMaterials (the LUT continues the
   // main thread's default-seeded RNG stream).
   Scene scene;
-  if (!scene.LoadScene(scene_path)) return 1;
+  if (scene_path.rfind("@api", 0) == 0) {
+    // "@api" or "@api:TEXTURE.bmp"
+    build_api_scene(&scene, scene_path.size() > 5 ? scene_path.c_str() + 5 : "");
+  } else if (!scene.LoadScene(scene_path)) {
+    return 1;
+  }
   InitializeMaterials();
 
   Camera cam(vector3(-5.80f, 7.05f, -47.06f), vector3(0.0f, 8.94f, 0.0f));  // main.cpp:87-88

@@ -18,6 +18,7 @@
 #include <sys/time.h>
 #include <algorithm>
 #include <memory>
+#include <utility>
 
 namespace base {
 typedef int64_t int64;
@@ -57,14 +58,17 @@ typedef double float64;
 #define sscanf_s sscanf      /* the extra size argument is ignored */
 
 /* Win32 min/max macros promote through the ternary operator; mirror that
- * (used at reference scene.cpp:39 and material.cpp:333). */
+ * (used at reference scene.cpp:39 and material.cpp:333).  The result type is
+ * decayed: for two lvalues of one type the conditional is an lvalue, and
+ * returning it by reference would dangle. */
+#include <type_traits>
 namespace base {
 template <class A, class B>
-inline auto min(A a, B b) -> decltype(a < b ? a : b) {
+inline typename std::decay<decltype(true ? std::declval<A>() : std::declval<B>())>::type min(A a, B b) {
   return a < b ? a : b;
 }
 template <class A, class B>
-inline auto max(A a, B b) -> decltype(a > b ? a : b) {
+inline typename std::decay<decltype(true ? std::declval<A>() : std::declval<B>())>::type max(A a, B b) {
   return a > b ? a : b;
 }
 }  // namespace base

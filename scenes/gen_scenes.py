@@ -319,11 +319,11 @@ def scene_mesh(outdir, nu, nv, name, aperture=0.0, knot=False):
     return s
 
 
-def scene_glass(outdir, aperture=0.0):
+def scene_glass(outdir, aperture=0.0, sky_size=(512, 256)):
     """Config 3: glass / frosted glass / liquid primitives, ceramic, env-map sky."""
-    sky = os.path.join(outdir, "sky.bmp")
+    sky = os.path.join(outdir, "sky_%dx%d.bmp" % sky_size)
     if not os.path.exists(sky):
-        sky_texture(sky)
+        sky_texture(sky, *sky_size)
     s = "# fs2-b200 glass + liquid scene under an environment texture (BASELINE config 3)\n"
     s += common_materials(outdir)
     s += material("env_mat", emission=(1.0, 1.0, 1.0), texture_scale=1.0, texture=sky)
@@ -370,6 +370,9 @@ SCENES = {
     "mesh_small": lambda d: scene_mesh(d, 64, 33, "small", knot=True),  # 4 096 tris/mesh + knot
     "mesh100k": lambda d: scene_mesh(d, 320, 161, "m100k"),           # 102 400 tris/mesh
     "glass": lambda d: scene_glass(d),
+    "glass_small": lambda d: scene_glass(d, sky_size=(64, 32)),
+    "glass_dof": lambda d: scene_glass(d, aperture=1.5),
+    "grid_tiny": lambda d: scene_grid(d, 24, 12, "gtiny", aperture=0.0),
     "grid_small": lambda d: scene_grid(d, 64, 32, "gsmall"),
     "grid4m": lambda d: scene_grid(d, 2048, 1024, "g4m"),
 }
