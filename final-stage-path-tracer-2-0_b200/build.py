@@ -65,8 +65,10 @@ def build_host(force=False):
     deps = srcs + _sources(HOST, (".h",)) + _sources(os.path.join(REPO_DIR, "include"), (".h",))
     if not force and not _newer(HOST_LIB, deps):
         return HOST_LIB
+    build_cuda()  # libfs2host.so links against the C ABI library next to it
     cmd = ["g++"] + GXX_FLAGS + ["-I" + os.path.join(REPO_DIR, "include"), "-I" + HOST,
-                                 "-o", HOST_LIB] + srcs + ["-ldl", "-lpthread"]
+                                 "-o", HOST_LIB] + srcs + ["-L" + PKG_DIR, "-lfs2cuda",
+                                                           "-Wl,-rpath,$ORIGIN", "-lpthread"]
     subprocess.run(cmd, check=True)
     return HOST_LIB
 

@@ -1,0 +1,29 @@
+// fs2_assets.h — .obj / .bmp / .hdr readers (see fs2_assets.cpp).
+#ifndef FS2_ASSETS_H_
+#define FS2_ASSETS_H_
+
+#include <stdint.h>
+
+#include <string>
+#include <vector>
+
+namespace fs2h {
+
+struct ObjData {
+  std::vector<float> positions;  // 3 per vertex
+  std::vector<float> normals;    // 3 per normal
+  std::vector<float> texcoords;  // 2 per texcoord
+  std::vector<int> corners;      // (vertex, normal, texcoord) per triangle corner; -1 = absent
+};
+
+struct Image {
+  uint32_t width = 0, height = 0;
+  std::vector<float> rgb;  // 3 floats per texel, rows in file order
+};
+
+bool load_obj(const std::string& path, ObjData* out, std::string* error);
+bool load_bmp(const std::string& path, Image* out);
+bool load_hdr(const std::string& path, Image* out);
+
+}  // namespace fs2h
+#endif

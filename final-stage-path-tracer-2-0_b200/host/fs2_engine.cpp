@@ -1,0 +1,223 @@
+// fs2_engine.cpp — DisplayFrame, TraceScene / TraceRange of the host mirror and the C
+// surface used from Python.  This is where the reference's seam (source/engine.h:68-75)
+// meets the C ABI: flatten-if-dirty -> fs_scene_upload -> fs_trace / fs_first_hit ->
+// fs_film_read into the DisplayFrame's host buffers.  No tracing happens on the host.
+#include <stdio.h>
+
+#include "fs2_impl.h"
+
+namespace {
+
+struct TraceState {
+  int device = 0;
+  uint64_t seed = 0x46533230ull;  // "FS20"
+  fs_ctx* ctx = nullptr;
+  int ctx_device = -1;
+  const void* scene = nullptr;  // SceneImpl whose flattening is resident on the device
+  uint64_t scene_version = 0;
+  const void* frame = nullptr;  // FrameImpl that owns the device film
+  uint32_t film_w = 0, film_h = 0;
+  char error[512] = "";
+};
+
+TraceState& state() {
+  static TraceState s;
+  return s;
+}
+
+int fail(const char* what, fs_ctx* ctx) {
+  TraceState& st = state();
+  snprintf(st.error, sizeof st.error, "%s: %s", what, fs_last_error(ctx));
+  fprintf(stderr, "fs2: %s\n", st.error);
+  return -1;
+}
+
+int ensure_context() {
+  TraceState& st = state();
+  if (st.ctx && st.ctx_device == st.device) return 0;
+  if (st.ctx) fs_destroy(st.ctx);
+  st.ctx = nullptr;
+  st.scene = nullptr;
+  st.frame = nullptr;
+  st.film_w = st.film_h = 0;
+  if (fs_create(&st.ctx, st.device, 0) != FS_OK) return fail("fs_create", nullptr);
+  st.ctx_device = st.device;
+  return 0;
+}
+
+int ensure_scene(base::Scene* scene) {
+  TraceState& st = state();
+  fs2h::SceneImpl* si = scene->impl();
+  const fs_scene_desc* d = scene->Flatten();
+  if (st.scene == si && st.scene_version == si->flat_version) return 0;
+  if (fs_scene_upload(st.ctx, d) != FS_OK) return fail("fs_scene_upload", st.ctx);
+  st.scene = si;
+  st.scene_version = si->flat_version;
+  return 0;
+}
+
+fs_camera to_pod(const base::Camera& c) {
+  fs_camera o;
+  memset(&o, 0, sizeof o);
+  o.origin[0] = c.origin.x;
+  o.origin[1] = c.origin.y;
+  o.origin[2] = c.origin.z;
+  o.target[0] = c.target.x;
+  o.target[1] = c.target.y;
+  o.target[2] = c.target.z;
+  o.fov_y = c.fov_y;
+  o.aperture_size = c.aperture_size;
+  o.focal_depth = c.focal_depth;
+  o.z_near = c.z_near;
+  o.z_far = c.z_far;
+  o.fast_render_enabled = c.fast_render_enabled ? 1 : 0;
+  return o;
+}
+
+}  // namespace
+
+namespace base {
+
+using namespace fs2h;
+
+// ---------------------------------------------------------------- DisplayFrame
+DisplayFrame::DisplayFrame(uint32 width, uint32 height) : impl_(new FrameImpl()) {
+  FrameImpl& f = *impl_;
+  f.width = width;
+  f.height = height;
+  size_t n = (size_t)width * height;
+  f.mean.assign(n * 3, 0.f);
+  f.normal.assign(n * 3, 0.f);
+  f.depth.assign(n, 0.f);
+  f.count.assign(n, 0);
+  f.rgb8.assign(n * 3, 0);
+  f.mat_id.assign(n, 0);
+}
+DisplayFrame::~DisplayFrame() {
+  if (state().frame == impl_.get()) state().frame = nullptr;
+}
+void DisplayFrame::Reset() {  // frame.cpp:43-51
+  FrameImpl& f = *impl_;
+  std::fill(f.mean.begin(), f.mean.end(), 0.f);
+  std::fill(f.normal.begin(), f.normal.end(), 0.f);
+  std::fill(f.depth.begin(), f.depth.end(), 0.f);
+  std::fill(f.count.begin(), f.count.end(), 0u);
+  std::fill(f.rgb8.begin(), f.rgb8.end(), (uint8_t)0);
+  std::fill(f.mat_id.begin(), f.mat_id.end(), (uint64_t)0);
+  f.samples = 0;
+  f.device_dirty = true;
+}
+uint8* DisplayFrame::GetDisplayBuffer() { return impl_->rgb8.data(); }
+uint32 DisplayFrame::GetWidth() { return impl_->width; }
+uint32 DisplayFrame::GetHeight() { return impl_->height; }
+float32 DisplayFrame::GetAspectRatio() { return (float32)impl_->width / impl_->height; }
+void DisplayFrame::SetFrameCount(uint32 count) { impl_->frame_count = count; }
+const float32* DisplayFrame::GetRenderTarget() { return impl_->mean.data(); }
+const uint32* DisplayFrame::GetCountBuffer() { return impl_->count.data(); }
+const float32* DisplayFrame::GetNormalBuffer() { return impl_->normal.data(); }
+const float32* DisplayFrame::GetDepthBuffer() { return impl_->depth.data(); }
+const uint64* DisplayFrame::GetMaterialIdBuffer() { return impl_->mat_id.data(); }
+
+// ---------------------------------------------------------------- tracing
+void SetTraceDevice(int device) { state().device = device; }
+void SetTraceSeed(uint64 seed) { state().seed = seed; }
+const char* LastTraceError() { return state().error; }
+
+int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 n_samples) {
+  if (!scene || !output) return -1;
+  TraceState& st = state();
+  if (ensure_context() || ensure_scene(scene)) return -1;
+  FrameImpl* f = output->impl();
+  if (st.film_w != f->width || st.film_h != f->height) {
+    if (fs_film_resize(st.ctx, (int)f->width, (int)f->height) != FS_OK)
+      return fail("fs_film_resize", st.ctx);
+    st.film_w = f->width;
+    st.film_h = f->height;
+    st.frame = f;
+    f->device_dirty = false;
+    f->samples = 0;
+  } else if (st.frame != f || f->device_dirty) {
+    // The device film accumulates for one DisplayFrame at a time.
+    if (fs_film_reset(st.ctx) != FS_OK) return fail("fs_film_reset", st.ctx);
+    st.frame = f;
+    f->device_dirty = false;
+    f->samples = 0;
+  }
+  fs_camera cam = to_pod(view);
+  if (fs_trace(st.ctx, &cam, f->samples, n_samples, 1, st.seed, FS_TRACE_DEFAULT) != FS_OK)
+    return fail("fs_trace", st.ctx);
+  f->samples += n_samples;
+  f->frame_count += n_samples;
+  if (fs_film_read(st.ctx, f->mean.data(), f->count.data(), f->rgb8.data(), f->normal.data(),
+                   f->depth.data(), f->mat_id.data()) != FS_OK)
+    return fail("fs_film_read", st.ctx);
+  return 0;
+}
+
+void TraceScene(const Camera& view, Scene* scene, DisplayFrame* output, ImagePlaneCache*) {
+  TraceSamples(view, scene, output, 1);
+}
+
+float32 TraceRange(const Camera& viewer, Scene* scene, DisplayFrame* frame, float32 x, float32 y) {
+  if (!scene || !frame) return 0.0f;
+  TraceState& st = state();
+  if (ensure_context() || ensure_scene(scene)) return viewer.z_far;
+  fs_camera cam = to_pod(viewer);
+  float range = viewer.z_far;
+  if (fs_trace_range(st.ctx, &cam, (int)frame->GetWidth(), (int)frame->GetHeight(), x, y,
+                     &range) != FS_OK) {
+    fail("fs_trace_range", st.ctx);
+    return viewer.z_far;
+  }
+  return range;
+}
+
+}  // namespace base
+
+// ================================================================= C surface (ctypes)
+extern "C" {
+
+void* fs2h_scene_new() { return new base::Scene(); }
+void fs2h_scene_free(void* s) { delete (base::Scene*)s; }
+int fs2h_scene_load(void* s, const char* path) { return ((base::Scene*)s)->LoadScene(path) ? 0 : -1; }
+void fs2h_initialize_materials() { base::InitializeMaterials(); }
+// Restarts the process-wide random stream at the reference's default state, so that a
+// scene loaded later in the same process gets the ids / normal table a fresh process would.
+void fs2h_reset_rng() { fs2h::main_rng() = fs2h::Xorshift(); }
+const fs_scene_desc* fs2h_scene_flatten(void* s) { return ((base::Scene*)s)->Flatten(); }
+int fs2h_scene_save_blob(void* s, const char* path) { return ((base::Scene*)s)->SaveBlob(path) ? 0 : -1; }
+int fs2h_scene_camera(void* s, int index, fs_camera* out) {
+  base::Camera* c = ((base::Scene*)s)->GetCamera((uint32_t)index);
+  base::Camera def(base::vector3(-5.80f, 7.05f, -47.06f), base::vector3(0.0f, 8.94f, 0.0f));
+  *out = to_pod(c ? *c : def);  // default viewpoint of reference source/main.cpp:87-88
+  return c ? 0 : 1;
+}
+void* fs2h_frame_new(uint32_t w, uint32_t h) { return new base::DisplayFrame(w, h); }
+void fs2h_frame_free(void* f) { delete (base::DisplayFrame*)f; }
+void fs2h_frame_reset(void* f) { ((base::DisplayFrame*)f)->Reset(); }
+const uint8_t* fs2h_frame_display(void* f) { return ((base::DisplayFrame*)f)->GetDisplayBuffer(); }
+const float* fs2h_frame_mean(void* f) { return ((base::DisplayFrame*)f)->GetRenderTarget(); }
+const uint32_t* fs2h_frame_count(void* f) { return ((base::DisplayFrame*)f)->GetCountBuffer(); }
+
+static base::Camera from_pod(const fs_camera* c) {
+  base::Camera cam(base::vector3(c->origin[0], c->origin[1], c->origin[2]),
+                   base::vector3(c->target[0], c->target[1], c->target[2]));
+  cam.fov_y = c->fov_y;
+  cam.aperture_size = c->aperture_size;
+  cam.focal_depth = c->focal_depth;
+  cam.z_near = c->z_near;
+  cam.z_far = c->z_far;
+  cam.fast_render_enabled = c->fast_render_enabled != 0;
+  return cam;
+}
+int fs2h_trace_samples(void* scene, const fs_camera* cam, void* frame, uint32_t n) {
+  return base::TraceSamples(from_pod(cam), (base::Scene*)scene, (base::DisplayFrame*)frame, n);
+}
+float fs2h_trace_range(void* scene, const fs_camera* cam, void* frame, float x, float y) {
+  return base::TraceRange(from_pod(cam), (base::Scene*)scene, (base::DisplayFrame*)frame, x, y);
+}
+void fs2h_set_device(int device) { base::SetTraceDevice(device); }
+void fs2h_set_seed(uint64_t seed) { base::SetTraceSeed(seed); }
+const char* fs2h_last_error() { return base::LastTraceError(); }
+
+}  // extern "C"

@@ -1,0 +1,267 @@
+// fs2_host.h — C++ host mirror of Final Stage 2.0's engine / scene / material / camera API
+// for the path-tracing hot path (libfs2host.so).
+//
+// Same names, argument meaning and ownership rules as the reference's public classes in
+// namespace base, so that code written against the reference (e.g. its main.cpp loop)
+// compiles against this header:
+//   Camera                         reference source/camera.h:43-63
+//   Material family                reference source/material.h:54-330
+//   Object family                  reference source/object.h:63-152, source/mesh.h:124-149
+//   Scene                          reference source/scene.h:94-185
+//   DisplayFrame                   reference source/frame.h:49-92
+//   TraceScene / TraceRange        reference source/engine.h:68-75
+// What differs is where the work happens: scene loading, octree construction and
+// flattening stay on the host (this library); ray generation, traversal, intersection,
+// shading and film accumulation run in libfs2cuda.so behind include/fs2_cabi.h.  There is
+// no CPU tracing path here: TraceScene fails loudly (prints + returns) without a GPU.
+#ifndef FS2_HOST_H_
+#define FS2_HOST_H_
+
+#include <stdint.h>
+
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "fs2_cabi.h"
+
+namespace fs2h {
+struct SceneImpl;
+struct MaterialImpl;
+struct ObjectImpl;
+struct FrameImpl;
+}  // namespace fs2h
+
+namespace base {
+
+typedef float float32;
+typedef uint8_t uint8;
+typedef uint32_t uint32;
+typedef int32_t int32;
+typedef uint64_t uint64;
+
+struct vector2 {
+  float32 x, y;
+  vector2() : x(0), y(0) {}
+  vector2(float32 a, float32 b) : x(a), y(b) {}
+};
+struct vector3 {
+  float32 x, y, z;
+  vector3() : x(0), y(0), z(0) {}
+  vector3(float32 a, float32 b, float32 c) : x(a), y(b), z(c) {}
+};
+struct vector4 {
+  float32 x, y, z, w;
+  vector4() : x(0), y(0), z(0), w(0) {}
+  vector4(float32 a, float32 b, float32 c, float32 d) : x(a), y(b), z(c), w(d) {}
+};
+typedef vector4 plane;
+
+// ---------------------------------------------------------------- camera
+class Camera {
+ public:
+  Camera();
+  Camera(const vector3& new_origin, const vector3& new_target);
+  vector3 origin;
+  vector3 target;
+  float32 fov_y;
+  float32 aperture_size;
+  float32 focal_depth;
+  float32 z_near;
+  float32 z_far;
+  bool fast_render_enabled;
+};
+
+// ---------------------------------------------------------------- materials
+// Host-side records only: Reflection()/Sample() are the CUDA kernels' job.
+class Material {
+ public:
+  virtual ~Material();
+  uint32 GetID() const;
+  virtual bool IsLight() const { return false; }
+  const fs_material& Record() const;
+  fs2h::MaterialImpl* impl() const { return impl_.get(); }
+
+ protected:
+  explicit Material(uint32_t type);  // draws the id from the process-wide stream
+  std::unique_ptr<fs2h::MaterialImpl> impl_;
+};
+
+class DiffuseMaterial : public Material {
+ public:
+  DiffuseMaterial();
+  explicit DiffuseMaterial(const vector3& diffuse);
+  explicit DiffuseMaterial(const std::string& filename, float32 tex_scale = 1.0f);
+  // .bmp as in the reference; .hdr (Radiance RGBE) is an extension; .exr is not supported
+  // in this build (the reference reads it through the vendored tinyexr).
+  void LoadDiffuseTexture(const std::string& filename, float32 tex_scale = 1.0f);
+
+ protected:
+  explicit DiffuseMaterial(uint32_t type);
+};
+
+class LightMaterial : public DiffuseMaterial {
+ public:
+  LightMaterial();
+  explicit LightMaterial(const vector3& emissive);
+  bool IsLight() const override { return true; }
+};
+class MetalMaterial : public DiffuseMaterial {
+ public:
+  MetalMaterial(const vector3& diffuse, float32 roughness);
+};
+class MirrorMaterial : public DiffuseMaterial {
+ public:
+  explicit MirrorMaterial(const vector3& diffuse);
+};
+class GlassMaterial : public DiffuseMaterial {
+ public:
+  GlassMaterial(const vector3 diffuse, float32 index = 0.75f, float32 reflectivity = 0.1f,
+                float32 frost = 0.0f);
+};
+class LiquidMaterial : public DiffuseMaterial {
+ public:
+  LiquidMaterial(const vector3 diffuse, float32 index = 0.75f, float32 reflectivity = 0.4f);
+};
+class CeramicMaterial : public DiffuseMaterial {
+ public:
+  CeramicMaterial(const vector3& diffuse, float32 shininess);
+
+ protected:
+  CeramicMaterial(uint32_t type, const vector3& diffuse, float32 shininess);
+};
+class GlowMaterial : public CeramicMaterial {
+ public:
+  GlowMaterial(const vector3& diffuse, const vector3& glow, float32 shininess);
+};
+class FogMaterial : public DiffuseMaterial {
+ public:
+  FogMaterial(const vector3 diffuse, float32 density);
+};
+
+// Fills the 32 K random-normal table from the process-wide stream (reference
+// source/material.cpp:17, source/math/normal.cpp:9-27).  Call once after the scene's
+// materials exist and before tracing, like the reference's main.cpp does.
+void InitializeMaterials();
+
+// ---------------------------------------------------------------- objects
+class Object {
+ public:
+  virtual ~Object();
+  void SetMaterial(std::shared_ptr<Material> material);
+  Material* GetMaterial() { return material_.get(); }
+  void GetBounds(vector3* bmin, vector3* bmax) const;
+  fs2h::ObjectImpl* impl() const { return impl_.get(); }
+
+ protected:
+  Object();
+  friend class Scene;
+  std::shared_ptr<Material> material_;
+  std::unique_ptr<fs2h::ObjectImpl> impl_;
+};
+class SphericalObject : public Object {
+ public:
+  SphericalObject(const vector3& origin, float32 radius);
+};
+class PlanarObject : public Object {
+ public:
+  explicit PlanarObject(const plane& data);
+};
+class DiscObject : public Object {
+ public:
+  DiscObject(const vector3& origin, const vector3& normal, float32 radius);
+};
+class CuboidObject : public Object {
+ public:
+  CuboidObject(const vector3& origin, float32 width, float32 height, float32 depth);
+  void Rotate(const vector3& axis, float32 angle);
+};
+class QuadObject : public Object {
+ public:
+  QuadObject(const vector3& origin, const vector3& normal, float32 width, float32 height);
+  QuadObject(const vector3& position, const vector3& u, const vector3& v);
+};
+class MeshObject : public Object {
+ public:
+  MeshObject(const std::string& filename, bool invert_normals = false,
+             const vector3& translation = vector3(0, 0, 0),
+             const vector3& scale = vector3(1, 1, 1),
+             const vector4& rotation = vector4(0, 0, 0, 0));
+};
+
+// ---------------------------------------------------------------- scene
+class Scene {
+ public:
+  Scene();
+  ~Scene();
+  bool LoadScene(const std::string& filename);
+  MeshObject* AddMeshObject(const std::string& filename, bool invert_normals = false,
+                            const vector3& translation = vector3(0, 0, 0),
+                            const vector3& scale = vector3(1, 1, 1),
+                            const vector4& rotation = vector4(0, 0, 0, 0));
+  SphericalObject* AddSphericalObject(const vector3& origin, float32 radius);
+  DiscObject* AddDiscObject(const vector3& origin, const vector3& normal, float32 radius);
+  PlanarObject* AddPlanarObject(const plane& data);
+  CuboidObject* AddCuboidObject(const vector3& origin, float32 width, float32 height,
+                                float32 depth);
+  QuadObject* AddQuadObject(const vector3& origin, const vector3& normal, float32 width,
+                            float32 height);
+  QuadObject* AddQuadObject(const vector3& position, const vector3& u, const vector3& v);
+  void SetSkyMaterial(std::shared_ptr<LightMaterial> material);
+  LightMaterial* GetSkyMaterial();
+  void Optimize();
+  uint32 GetCameraCount();
+  Camera* GetCamera(uint32 index);
+
+  // ---- additions for the GPU path
+  // Flattens objects, octrees, materials, textures and the normal table into the arrays
+  // of include/fs2_cabi.h.  The returned description stays valid until the scene changes.
+  const fs_scene_desc* Flatten();
+  bool SaveBlob(const std::string& path);  // include/fs2_blob.h
+  fs2h::SceneImpl* impl() { return impl_.get(); }
+
+ private:
+  std::unique_ptr<fs2h::SceneImpl> impl_;
+};
+
+// ---------------------------------------------------------------- film
+class ImagePlaneCache;  // accepted and ignored (dead code in the reference, engine.cpp:33-57)
+
+class DisplayFrame {
+ public:
+  DisplayFrame(uint32 width, uint32 height);
+  ~DisplayFrame();
+  void Reset();
+  uint8* GetDisplayBuffer();
+  uint32 GetWidth();
+  uint32 GetHeight();
+  float32 GetAspectRatio();
+  void SetFrameCount(uint32 count);
+  // ---- additions: read access to the buffers the reference keeps private (frame.h:79-91)
+  const float32* GetRenderTarget();     // float mean, 3 per pixel
+  const uint32* GetCountBuffer();
+  const float32* GetNormalBuffer();
+  const float32* GetDepthBuffer();
+  const uint64* GetMaterialIdBuffer();
+  fs2h::FrameImpl* impl() { return impl_.get(); }
+
+ private:
+  std::unique_ptr<fs2h::FrameImpl> impl_;
+};
+
+// One sample per pixel appended to `output` (never cleared here), like the reference.
+void TraceScene(const Camera& view, Scene* scene, DisplayFrame* output,
+                ImagePlaneCache* cache = nullptr);
+// Distance to the object seen at fractional pixel (x, y); z_far on a miss.
+float32 TraceRange(const Camera& viewer, Scene* scene, DisplayFrame* frame, float32 x, float32 y);
+
+// ---- additions
+// n samples per pixel in one launch (TraceScene == TraceSamples(…, 1)).
+int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 n_samples);
+// Selects the CUDA device used by TraceScene/TraceRange (default 0) and the seed.
+void SetTraceDevice(int device);
+void SetTraceSeed(uint64 seed);
+const char* LastTraceError();
+
+}  // namespace base
+#endif
