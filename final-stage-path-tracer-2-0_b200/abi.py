@@ -19,6 +19,7 @@ FS_TRACE_NO_JITTER = 1
 FS_TRACE_NO_DOF = 2
 FS_TRACE_WAVEFRONT = 4
 FS_TRACE_NO_RESOLVE = 8
+FS_TRACE_ASYNC = 16
 
 # numpy dtypes of the flattened arrays -------------------------------------------------
 NODE_DT = np.dtype([("bmin", "<f4", 3), ("first", "<u4"), ("bmax", "<f4", 3), ("count", "<u4")])
@@ -66,7 +67,7 @@ class fs_stats(C.Structure):
     _fields_ = [("n_paths", C.c_uint64), ("n_segments", C.c_uint64), ("n_node", C.c_uint64),
                 ("n_tri", C.c_uint64), ("n_bary", C.c_uint64), ("n_prim", C.c_uint64),
                 ("n_shade", C.c_uint64), ("launches", C.c_uint64), ("last_trace_ms", C.c_float),
-                ("pad", C.c_float)]
+                ("last_kernel_ms", C.c_float)]
 
 
 def make_camera(origin=(-5.80, 7.05, -47.06), target=(0.0, 8.94, 0.0), fov_y=45.0,

@@ -32,8 +32,10 @@ struct DeviceBuf {
 
 struct fs_ctx {
   int device = 0;
-  cudaStream_t stream = nullptr;
-  cudaEvent_t ev0 = nullptr, ev1 = nullptr;
+  cudaStream_t stream = nullptr;      // stream in use
+  cudaStream_t own_stream = nullptr;  // created by fs_create
+  cudaEvent_t ev0 = nullptr, ev1 = nullptr, evk0 = nullptr, evk1 = nullptr;
+  bool timing_pending = false;
   char error[512] = "";
   // scene
   bool have_scene = false;
@@ -47,7 +49,7 @@ struct fs_ctx {
   // stats
   unsigned long long* d_stats = nullptr;
   uint64_t launches = 0;
-  float last_trace_ms = 0.f;
+  float last_trace_ms = 0.f, last_kernel_ms = 0.f;
   bool stats_build = false;
 };
 
@@ -217,6 +219,15 @@ int set_device(fs_ctx* ctx) {
 
 dim3 pixel_grid(int w, int h) { return dim3((w + 15) / 16, (h + 7) / 8); }
 
+// Reads the event pairs of the last fs_trace; the stream must have been synchronised.
+int collect_timing(fs_ctx* ctx) {
+  if (!ctx->timing_pending) return FS_OK;
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->last_trace_ms, ctx->ev0, ctx->ev1));
+  CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->last_kernel_ms, ctx->evk0, ctx->evk1));
+  ctx->timing_pending = false;
+  return FS_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -240,9 +251,12 @@ int fs_create(fs_ctx** out, int device, int flags) {
   ctx->stats_build = (flags & 1) != 0;
   int rc = set_device(ctx);
   if (rc == FS_OK) {
-    cudaError_t e1 = cudaStreamCreateWithFlags(&ctx->stream, cudaStreamNonBlocking);
+    cudaError_t e1 = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
+    ctx->stream = ctx->own_stream;
     if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->ev0);
     if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->ev1);
+    if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->evk0);
+    if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->evk1);
     if (e1 == cudaSuccess) e1 = cudaMalloc(&ctx->d_stats, ST_COUNT * sizeof(unsigned long long));
     if (e1 == cudaSuccess)
       e1 = cudaMemset(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long));
@@ -268,7 +282,9 @@ int fs_destroy(fs_ctx* ctx) {
   if (ctx->d_stats) cudaFree(ctx->d_stats);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
-  if (ctx->stream) cudaStreamDestroy(ctx->stream);
+  if (ctx->evk0) cudaEventDestroy(ctx->evk0);
+  if (ctx->evk1) cudaEventDestroy(ctx->evk1);
+  if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
   delete ctx;
   return FS_OK;
 }
@@ -350,8 +366,7 @@ int fs_film_reset(fs_ctx* ctx) {
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->mean.p, 0, n * 12, ctx->stream));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->count.p, 0, n * 4, ctx->stream));
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->rgb8.p, 0, n * 3, ctx->stream));
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  return FS_OK;
+  return FS_OK;  // stream-ordered with the launches that follow
 }
 
 int fs_first_hit(fs_ctx* ctx, const fs_camera* cam, int width, int height, float* t,
@@ -446,6 +461,7 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
             ctx->height};
   TraceParams tp{first_sample, n_samples, sample_stride, seed, flags};
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
+  CUDA_TRY(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
   if (n_samples) {
     dim3 grid = pixel_grid(ctx->width, ctx->height);
     if (ctx->stats_build)
@@ -455,6 +471,7 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
   }
+  CUDA_TRY(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
   if (!(flags & FS_TRACE_NO_RESOLVE)) {
     int n = ctx->width * ctx->height;
     k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(
@@ -464,9 +481,10 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
     CUDA_TRY(ctx, cudaGetLastError());
   }
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev1, ctx->stream));
+  ctx->timing_pending = true;
+  if (flags & FS_TRACE_ASYNC) return FS_OK;
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  CUDA_TRY(ctx, cudaEventElapsedTime(&ctx->last_trace_ms, ctx->ev0, ctx->ev1));
-  return FS_OK;
+  return collect_timing(ctx);
 }
 
 int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8, float* normal,
@@ -517,6 +535,7 @@ int fs_get_stats(fs_ctx* ctx, fs_stats* out) {
   unsigned long long h[ST_COUNT];
   CUDA_TRY(ctx, cudaMemcpyAsync(h, ctx->d_stats, sizeof h, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if ((rc = collect_timing(ctx))) return rc;
   memset(out, 0, sizeof *out);
   out->n_paths = h[ST_PATHS];
   out->n_segments = h[ST_SEGMENTS];
@@ -527,6 +546,7 @@ int fs_get_stats(fs_ctx* ctx, fs_stats* out) {
   out->n_shade = h[ST_SHADE];
   out->launches = ctx->launches;
   out->last_trace_ms = ctx->last_trace_ms;
+  out->last_kernel_ms = ctx->last_kernel_ms;
   return FS_OK;
 }
 
@@ -537,6 +557,16 @@ int fs_reset_stats(fs_ctx* ctx) {
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   ctx->launches = 0;
+  return FS_OK;
+}
+
+int fs_set_stream(fs_ctx* ctx, void* stream) {
+  if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  if ((rc = collect_timing(ctx))) return rc;
+  ctx->stream = stream ? (cudaStream_t)stream : ctx->own_stream;
   return FS_OK;
 }
 

@@ -27,6 +27,7 @@ _SYMBOLS = {
     "fs_get_stats": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_stats)]),
     "fs_reset_stats": (C.c_int, [C.c_void_p]),
     "fs_get_stream": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p)]),
+    "fs_set_stream": (C.c_int, [C.c_void_p, C.c_void_p]),
 }
 
 _lib = None
@@ -165,10 +166,14 @@ class Context:
         self._check(self.lib.fs_get_stream(self.handle, C.byref(p)))
         return p.value or 0
 
+    def set_stream(self, stream):
+        """Enqueue on a caller-owned CUDA stream (integer handle); None restores the own one."""
+        self._check(self.lib.fs_set_stream(self.handle, C.c_void_p(stream) if stream else None))
+
     def stats(self):
         s = abi.fs_stats()
         self._check(self.lib.fs_get_stats(self.handle, C.byref(s)))
-        return {k: getattr(s, k) for k, _ in abi.fs_stats._fields_ if k != "pad"}
+        return {k: getattr(s, k) for k, _ in abi.fs_stats._fields_}
 
     def reset_stats(self):
         self._check(self.lib.fs_reset_stats(self.handle))

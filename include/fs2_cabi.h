@@ -193,6 +193,7 @@ typedef struct fs_camera {
 #define FS_TRACE_NO_DOF 2     /* ignore aperture_size                            */
 #define FS_TRACE_WAVEFRONT 4  /* use the wavefront pipeline instead of the megakernel */
 #define FS_TRACE_NO_RESOLVE 8 /* skip the mean/gamma resolve (multi-GPU: resolve after the reduce) */
+#define FS_TRACE_ASYNC 16     /* enqueue only: no stream synchronisation before returning */
 
 typedef struct fs_stats {
   uint64_t n_paths;    /* camera paths traced since the last reset           */
@@ -203,8 +204,8 @@ typedef struct fs_stats {
   uint64_t n_prim;     /* primitive (non-mesh object) tests                  */
   uint64_t n_shade;    /* material evaluations + sky lookups                 */
   uint64_t launches;   /* kernels launched by this context since the last reset */
-  float last_trace_ms; /* device time of the last fs_trace (CUDA events)     */
-  float pad;
+  float last_trace_ms;  /* device time of the last fs_trace, all its kernels (CUDA events) */
+  float last_kernel_ms; /* device time of the path-tracing kernel(s) alone in that call   */
 } fs_stats;
 
 typedef struct fs_ctx fs_ctx;
@@ -263,8 +264,11 @@ int fs_film_resolve(fs_ctx* ctx);
 int fs_get_stats(fs_ctx* ctx, fs_stats* out);
 int fs_reset_stats(fs_ctx* ctx);
 
-/* Current CUDA stream the context launches on (cudaStream_t as void*). */
+/* CUDA stream the context launches on (cudaStream_t as void*).  fs_set_stream makes the
+ * context enqueue on a caller-owned stream (e.g. the one an NCCL reduce of the film runs
+ * on); NULL restores the context's own stream. */
 int fs_get_stream(fs_ctx* ctx, void** stream);
+int fs_set_stream(fs_ctx* ctx, void* stream);
 
 #ifdef __cplusplus
 }

@@ -1,33 +1,38 @@
 #!/usr/bin/env python3
-"""Quick device-side timing probe: python scripts/probe.py BLOB W H SPP [stats]"""
+"""Quick device-side timing probe: python scripts/probe.py SCENE_NAME W H SPP [stats] [reps]
+SCENE_NAME is a key of scenes/gen_scenes.py (generated into scenes/_cache and loaded through
+the C++ host library)."""
 import os
 import sys
 import time
 
-sys.path.insert(0, os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, REPO)
+sys.path.insert(0, os.path.join(REPO, "scenes"))
 import fs2_b200
-from fs2_b200 import abi
+from fs2_b200 import host
+import gen_scenes
 
-blob, w, h, spp = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
+name, w, h, spp = sys.argv[1], int(sys.argv[2]), int(sys.argv[3]), int(sys.argv[4])
 stats = len(sys.argv) > 5 and sys.argv[5] == "stats"
-scene = abi.FlatScene.load(blob)
-cam = abi.camera_from_file(blob + ".camera")
-ctx = fs2_b200.Context(0, stats=stats)
+reps = int(sys.argv[6]) if len(sys.argv) > 6 else 3
+path = gen_scenes.generate(os.path.join(REPO, "scenes", "_cache"), [name])[name]
 t0 = time.time()
-ctx.upload(scene)
-print("upload %.3fs (%.1f MB)" % (time.time() - t0, scene.nbytes() / 1e6))
+hs = host.HostScene(path)
+desc = hs.desc()
+print("host load+build %.2fs (%.1f MB)" % (time.time() - t0, hs.nbytes() / 1e6))
+cam = hs.camera()
+ctx = fs2_b200.Context(0, stats=stats)
+ctx.upload(desc)
 ctx.resize(w, h)
 ctx.trace(cam, 1, seed=1)
-for rep in range(3):
+for rep in range(reps):
     ctx.reset()
     ctx.reset_stats()
-    t0 = time.time()
     ctx.trace(cam, spp, seed=2 + rep)
-    wall = time.time() - t0
     st = ctx.stats()
-    ms = st["last_trace_ms"]
-    print("rep %d: %.2f ms device (%.2f wall)  %.2f Mpaths/s  %.2f Mrays/s  seg/path %.2f" %
-          (rep, ms, wall * 1e3, st["n_paths"] / ms / 1e3, st["n_segments"] / ms / 1e3,
-           st["n_segments"] / st["n_paths"]), {k: v for k, v in st.items() if k.startswith("n_")})
-fh = ctx.first_hit(cam, w, h)
-print("first-hit coverage %.3f" % (fh["object"] != 0xFFFFFFFF).mean())
+    ms = st["last_kernel_ms"]
+    print("rep %d: %.2f ms kernel (%.2f total)  %.2f Mpaths/s  %.2f Mrays/s  seg/path %.2f" %
+          (rep, ms, st["last_trace_ms"], st["n_paths"] / ms / 1e3, st["n_segments"] / ms / 1e3,
+           st["n_segments"] / st["n_paths"]),
+          {k: v for k, v in st.items() if k.startswith("n_")} if stats else "")

@@ -1,0 +1,56 @@
+"""Host-side logic of the multi-GPU path on CPU: sample sharding and the film reduce over a
+world_size-2 gloo group (the GPU path runs the same functions over NCCL)."""
+import os
+import sys
+
+import numpy as np
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+import fs2_b200
+from fs2_b200 import multi_gpu
+
+
+def test_shard_samples_partitions_exactly():
+    for total in (0, 1, 7, 64, 257):
+        for world in (1, 2, 3, 4, 8):
+            seen = []
+            for r in range(world):
+                first, n, stride = multi_gpu.shard_samples(total, r, world)
+                seen += [first + k * stride for k in range(n)]
+            assert sorted(seen) == list(range(total))
+            sizes = [multi_gpu.shard_samples(total, r, world)[1] for r in range(world)]
+            assert max(sizes) - min(sizes) <= 1
+
+
+def _worker(rank, world, port, out_dir):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    n_px, total = 500, 10
+    rng = np.random.RandomState(123)
+    samples = rng.rand(total, n_px, 3).astype(np.float32)  # every rank knows all samples
+    first, n, stride = multi_gpu.shard_samples(total, rank, world)
+    film = torch.zeros(n_px, 4)
+    for k in range(n):
+        film[:, :3] += torch.from_numpy(samples[first + k * stride])
+        film[:, 3] += 1
+    flat = film.reshape(-1)
+    multi_gpu.reduce_film(flat, 0)
+    if rank == 0:
+        np.save(os.path.join(out_dir, "film.npy"), flat.reshape(n_px, 4).numpy())
+        np.save(os.path.join(out_dir, "want.npy"), samples.sum(0))
+    dist.barrier()
+    dist.destroy_process_group()
+
+
+def test_film_reduce_world2_gloo(tmp_path):
+    port = 29500 + (os.getpid() % 2000)
+    mp.spawn(_worker, args=(2, port, str(tmp_path)), nprocs=2, join=True)
+    film = np.load(tmp_path / "film.npy")
+    want = np.load(tmp_path / "want.npy")
+    assert (film[:, 3] == 10).all()
+    assert np.allclose(film[:, :3], want, rtol=1e-5, atol=1e-5)
+    mean = film[:, :3] / film[:, 3:4]
+    assert np.allclose(mean, want / 10, rtol=1e-5, atol=1e-6)
