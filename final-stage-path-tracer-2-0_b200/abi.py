@@ -20,6 +20,7 @@ FS_TRACE_NO_DOF = 2
 FS_TRACE_WAVEFRONT = 4
 FS_TRACE_NO_RESOLVE = 8
 FS_TRACE_ASYNC = 16
+FS_TRACE_PER_THREAD = 32
 
 # numpy dtypes of the flattened arrays -------------------------------------------------
 NODE_DT = np.dtype([("bmin", "<f4", 3), ("first", "<u4"), ("bmax", "<f4", 3), ("count", "<u4")])

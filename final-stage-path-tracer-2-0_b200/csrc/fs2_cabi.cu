@@ -464,10 +464,15 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
   CUDA_TRY(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
   if (n_samples) {
     dim3 grid = pixel_grid(ctx->width, ctx->height);
-    if (ctx->stats_build)
+    const bool per_thread = (flags & FS_TRACE_PER_THREAD) != 0;
+    if (ctx->stats_build && per_thread)
       k_trace_mega<true><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
-    else
+    else if (per_thread)
       k_trace_mega<false><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
+    else if (ctx->stats_build)
+      k_trace_coop<true><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
+    else
+      k_trace_coop<false><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
   }

@@ -5,6 +5,7 @@
 //                 persistent per-pixel thread with path regeneration
 //   k_resolve     DisplayFrame::WritePixel's mean / gamma / quantise (source/frame.cpp:53-76)
 #pragma once
+#include "fs2_coop.cuh"
 #include "fs2_shade.cuh"
 
 namespace fs2 {
@@ -74,148 +75,213 @@ k_first_hit(DScene S, CamBasis cam, int width, int height, float* __restrict__ o
   warp_add(stats + ST_PRIM, c.n_prim);
 }
 
-// One thread owns one pixel and renders its n_samples paths back to back; a finished
-// path is replaced by the pixel's next sample inside the same loop iteration, so the
-// warp only diverges inside a segment, never across path lengths.
+// ------------------------------------------------------------------ path state
+struct PathState {
+  V3 sum;  // radiance of the finished paths of this launch
+  V3 L, T;
+  uint32_t s, depth;
+  Rng rng;
+  Ray ray;
+  // depth-0 fog decision waits for the next hit position (material.cpp:330-337)
+  bool fog_pending;
+  V3 fog_pos;
+  uint32_t fog_mat;
+};
+
+// reference source/engine.cpp:205-244: jittered camera ray (+ thin lens) of the next sample
+__device__ __forceinline__ void begin_path(const CamBasis& cam, const TraceParams& tp,
+                                           uint32_t pixel, int px, int py, PathState& ps) {
+  uint32_t sample = tp.first_sample + ps.s * tp.sample_stride;
+  ps.rng = seed_rng(tp.seed, pixel, sample);
+  float jx = 0.f, jy = 0.f;
+  if (!(tp.flags & FS_TRACE_NO_JITTER)) {
+    jx = ps.rng.uniform() - 0.5f;
+    jy = ps.rng.uniform() - 0.5f;
+  }
+  ps.ray = camera_ray(cam, (float)px, (float)py, jx, jy);
+  if (cam.aperture > 0.0f && !(tp.flags & FS_TRACE_NO_DOF)) apply_dof(cam, ps.rng, ps.ray);
+  ps.L = v3(0.f, 0.f, 0.f);
+  ps.T = v3(1.f, 1.f, 1.f);
+  ps.depth = 0;
+  ps.fog_pending = false;
+}
+
+// Everything TraceStep does around Scene::Trace (reference source/engine.cpp:59-159) for the
+// segment whose nearest hit is `h`, in forward form; then either the next segment's ray is
+// in ps.ray, or the path is finished and the pixel's next sample (if any) is started.
+// Returns false when the lane has rendered all its samples.  The aux buffers of the film
+// are written by the last sample of the launch (frame.cpp:78-85: last sample wins).
+__device__ __forceinline__ bool finish_segment(const DScene& S, const CamBasis& cam,
+                                               const Film& film, const TraceParams& tp,
+                                               uint32_t pixel, int px, int py, PathState& ps,
+                                               const Hit& h, uint32_t& n_shade) {
+  const bool got = h.object != 0xFFFFFFFFu;
+  const bool last = ps.s + 1 == tp.n_samples;
+  bool done = false;
+
+  if (ps.fog_pending) {
+    // FogMaterial::Sample at depth 0: light_pos is the next hit position, or the segment
+    // end on a miss (engine.cpp:89-91).
+    ps.fog_pending = false;
+    V3 light_pos = got ? (ps.ray.start + ps.ray.dir * h.param) : ps.ray.stop;
+    float dist = length(ps.fog_pos - light_pos);
+    Mat fm = load_material(S, ps.fog_mat);
+    float a = (dist * dist) * fm.density * 0.00005f;
+    float threshold = saturate01(0.0f > a ? 0.0f : a);
+    if (ps.rng.uniform() < threshold) {
+      ps.L = fm.diffuse;
+      done = true;
+    }
+  }
+
+  if (!done && !got) {
+    // engine.cpp:88-102
+    V3 view = normalize(ps.ray.stop - ps.ray.start);
+    ps.L = ps.L + ps.T * sample_sky(S, view);
+    n_shade++;
+    if (ps.depth == 0 && last) {
+      V3 n = normalize(ps.ray.dir);
+      film.aux[pixel] = make_float4(n.x, n.y, n.z, cam.z_far);
+      film.mat_id[pixel] = __float_as_uint(__ldg(S.materials + 4 * (size_t)S.sky_material).y);
+    }
+    done = true;
+  } else if (!done) {
+    Mat m = load_material(S, __float_as_uint(obj_word(S, h.object, 0).y));
+    Surface sf = make_surface(S, ps.ray, h, m.texture >= 0);
+    V3 view = normalize(sf.point - ps.ray.start);
+    Bounce b = shade_surface(S, m, ps.rng, view, sf.normal, sf.u, sf.v);
+    n_shade++;
+    V3 add = b.add;
+    if (ps.depth == 0) {
+      // engine.cpp:147-156
+      if (m.type == FS_MAT_LIGHT && length(add) > 10.0f) add = normalize(add) * 10.0f;
+      if (last) {
+        film.aux[pixel] = make_float4(sf.normal.x, sf.normal.y, sf.normal.z,
+                                      length(ps.ray.start - sf.point));
+        film.mat_id[pixel] = m.id;
+      }
+      if (m.type == FS_MAT_FOG) {
+        ps.fog_pending = true;
+        ps.fog_pos = sf.point;
+        ps.fog_mat = sf.material;
+      }
+    }
+    ps.L = ps.L + ps.T * add;
+    if (!b.recurse) {
+      done = true;
+    } else {
+      ps.T = ps.T * b.weight;
+      ps.depth++;
+      if (ps.depth >= 8u) {
+        done = true;  // engine.cpp:62-64: black beyond kMaximumTraceDepth
+      } else if (cam.fast_render && ps.depth > 1u) {
+        ps.L = ps.L + ps.T;  // engine.cpp:68-70
+        done = true;
+      } else {
+        // engine.cpp:120-127
+        V3 off = b.dir * 0.03f;
+        V3 stop = sf.point + b.dir * cam.z_far;
+        ps.ray.start = sf.point + off;
+        ps.ray.stop = stop;
+        ps.ray.dir = (stop - sf.point) - off;
+        ps.ray.zero_length = near_zero(length(ps.ray.dir));
+      }
+    }
+  }
+
+  if (done) {
+    ps.sum = ps.sum + ps.L;
+    ps.s++;
+    if (ps.s == tp.n_samples) return false;
+    begin_path(cam, tp, pixel, px, py, ps);
+  }
+  return true;
+}
+
+__device__ __forceinline__ void film_add(const Film& film, uint32_t pixel, V3 sum, uint32_t n) {
+  float4 acc = film.sum[pixel];
+  acc.x += sum.x;
+  acc.y += sum.y;
+  acc.z += sum.z;
+  acc.w += (float)n;
+  film.sum[pixel] = acc;
+}
+
+// Variant A — one thread owns one pixel, walks its own leaves (kept for the ncu comparison
+// and as the FS_TRACE_PER_THREAD path).  A finished path is replaced by the pixel's next
+// sample inside the same loop iteration, so the warp only diverges inside a segment.
 template <bool STATS>
 __global__ void __launch_bounds__(128)
 k_trace_mega(DScene S, CamBasis cam, Film film, TraceParams tp,
              unsigned long long* __restrict__ stats) {
   int px, py;
-  bool alive = pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0;
-  const uint32_t pixel = alive ? (uint32_t)(py * film.width + px) : 0u;
+  const bool mine = pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0;
+  const uint32_t pixel = mine ? (uint32_t)(py * film.width + px) : 0u;
   Counters c = {0, 0, 0, 0};
   uint32_t n_seg = 0, n_shade = 0;
-
-  V3 sum = v3(0.f, 0.f, 0.f);
-  V3 L = v3(0.f, 0.f, 0.f), T = v3(1.f, 1.f, 1.f);
-  uint32_t s = 0, depth = 0;
-  Rng rng;
-  Ray ray;
-  // depth-0 fog decision waits for the next hit position (material.cpp:330-337)
-  bool fog_pending = false;
-  V3 fog_pos = v3(0.f, 0.f, 0.f);
-  uint32_t fog_mat = 0;
-  // aux of the current path (TraceResult, frame.h:40-47)
-  V3 aux_n = v3(0.f, 0.f, 0.f);
-  float aux_depth = 0.f;
-  uint32_t aux_mat = 0;
-
-  auto begin_path = [&]() {
-    uint32_t sample = tp.first_sample + s * tp.sample_stride;
-    rng = seed_rng(tp.seed, pixel, sample);
-    float jx = 0.f, jy = 0.f;
-    if (!(tp.flags & FS_TRACE_NO_JITTER)) {
-      jx = rng.uniform() - 0.5f;
-      jy = rng.uniform() - 0.5f;
-    }
-    ray = camera_ray(cam, (float)px, (float)py, jx, jy);
-    if (cam.aperture > 0.0f && !(tp.flags & FS_TRACE_NO_DOF)) apply_dof(cam, rng, ray);
-    L = v3(0.f, 0.f, 0.f);
-    T = v3(1.f, 1.f, 1.f);
-    depth = 0;
-    fog_pending = false;
-  };
-  if (alive) begin_path();
-
+  PathState ps;
+  ps.sum = v3(0.f, 0.f, 0.f);
+  ps.s = 0;
+  bool alive = mine;
+  if (alive) begin_path(cam, tp, pixel, px, py, ps);
   while (alive) {
-    Hit h = scene_trace<STATS>(S, ray, c);
+    Hit h = scene_trace<STATS>(S, ps.ray, c);
     n_seg++;
-    bool got = h.object != 0xFFFFFFFFu;
-    bool done = false;
+    alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, h, n_shade);
+  }
+  if (mine) film_add(film, pixel, ps.sum, tp.n_samples);
+  warp_add(stats + ST_PATHS, mine ? ps.s : 0u);
+  warp_add(stats + ST_SEGMENTS, n_seg);
+  warp_add(stats + ST_SHADE, n_shade);
+  if (STATS) {
+    warp_add(stats + ST_NODE, c.n_node);
+    warp_add(stats + ST_TRI, c.n_tri);
+    warp_add(stats + ST_BARY, c.n_bary);
+    warp_add(stats + ST_PRIM, c.n_prim);
+  }
+}
 
-    if (fog_pending) {
-      // FogMaterial::Sample at depth 0 (material.cpp:330-337): light_pos is the next hit
-      // position, or the segment end on a miss (engine.cpp:89-91).
-      fog_pending = false;
-      V3 light_pos = got ? (ray.start + ray.dir * h.param) : ray.stop;
-      float dist = length(fog_pos - light_pos);
-      Mat fm = load_material(S, fog_mat);
-      float a = (dist * dist) * fm.density * 0.00005f;
-      float threshold = saturate01(0.0f > a ? 0.0f : a);
-      if (rng.uniform() < threshold) {
-        L = fm.diffuse;
-        done = true;
-      }
-    }
-
-    if (!done && !got) {
-      // engine.cpp:88-102
-      V3 view = normalize(ray.stop - ray.start);
-      L = L + T * sample_sky(S, view);
-      n_shade++;
-      if (depth == 0) {
-        aux_n = normalize(ray.dir);
-        aux_depth = cam.z_far;
-        aux_mat = S.sky_material;
-      }
-      done = true;
-    } else if (!done) {
-      Mat m = load_material(S, __float_as_uint(obj_word(S, h.object, 0).y));
-      Surface sf = make_surface(S, ray, h, m.texture >= 0);
-      V3 view = normalize(sf.point - ray.start);
-      Bounce b = shade_surface(S, m, rng, view, sf.normal, sf.u, sf.v);
-      n_shade++;
-      V3 add = b.add;
-      if (depth == 0) {
-        // engine.cpp:147-156
-        if (m.type == FS_MAT_LIGHT && length(add) > 10.0f) add = normalize(add) * 10.0f;
-        aux_n = sf.normal;
-        aux_depth = length(ray.start - sf.point);
-        aux_mat = sf.material;
-        if (m.type == FS_MAT_FOG) {
-          fog_pending = true;
-          fog_pos = sf.point;
-          fog_mat = sf.material;
-        }
-      }
-      L = L + T * add;
-      if (!b.recurse) {
-        done = true;
-      } else {
-        T = T * b.weight;
-        depth++;
-        if (depth >= 8u) {
-          done = true;  // engine.cpp:62-64: black beyond kMaximumTraceDepth
-        } else if (cam.fast_render && depth > 1u) {
-          L = L + T;  // engine.cpp:68-70
-          done = true;
-        } else {
-          // engine.cpp:120-127
-          V3 start = sf.point + b.dir * 0.03f;
-          V3 stop = sf.point + b.dir * cam.z_far;
-          Ray nr;
-          nr.start = start;
-          nr.stop = stop;
-          nr.dir = (stop - sf.point) - (b.dir * 0.03f);
-          nr.zero_length = near_zero(length(nr.dir));
-          ray = nr;
-        }
-      }
-    }
-
-    if (done) {
-      sum = sum + L;
-      s++;
-      if (s == tp.n_samples) {
-        alive = false;
-      } else {
-        begin_path();
-      }
+// Variant B (default) — same per-pixel ownership and path regeneration, but the traversal
+// of every lane is a resumable state machine and mesh leaves are scanned by the whole warp
+// (fs2_coop.cuh).
+template <bool STATS>
+__global__ void __launch_bounds__(128)
+k_trace_coop(DScene S, CamBasis cam, Film film, TraceParams tp,
+             unsigned long long* __restrict__ stats) {
+  int px, py;
+  const bool mine = pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0;
+  const uint32_t pixel = mine ? (uint32_t)(py * film.width + px) : 0u;
+  Counters c = {0, 0, 0, 0};
+  uint32_t n_seg = 0, n_shade = 0;
+  PathState ps;
+  ps.sum = v3(0.f, 0.f, 0.f);
+  ps.s = 0;
+  ps.ray = make_ray(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f));
+  Frame sstack[FS2_SCENE_STACK];
+  Frame mstack[FS2_MESH_STACK];
+  LaneWalk w;
+  w.pc = PC_IDLE;
+  w.rec = no_hit();
+  w.glob = no_hit();
+  w.ret = false;
+  w.resume = false;
+  w.leaf_first = w.leaf_count = 0;
+  w.cur_obj = 0;
+  if (mine) {
+    begin_path(cam, tp, pixel, px, py, ps);
+    w.pc = PC_SEG_START;
+  }
+  while (__any_sync(0xFFFFFFFFu, w.pc != PC_IDLE)) {
+    lane_advance<STATS>(S, w, ps.ray, sstack, mstack, c);
+    warp_scan_leaves<STATS>(S, w, ps.ray, c);
+    if (w.pc == PC_SEG_DONE) {
+      n_seg++;
+      bool alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, w.rec, n_shade);
+      w.pc = alive ? PC_SEG_START : PC_IDLE;
     }
   }
-
-  if (pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0) {
-    float4 acc = film.sum[pixel];
-    acc.x += sum.x;
-    acc.y += sum.y;
-    acc.z += sum.z;
-    acc.w += (float)tp.n_samples;
-    film.sum[pixel] = acc;
-    film.aux[pixel] = make_float4(aux_n.x, aux_n.y, aux_n.z, aux_depth);
-    film.mat_id[pixel] = __float_as_uint(__ldg(S.materials + 4 * (size_t)aux_mat).y);
-  }
-  warp_add(stats + ST_PATHS, s);
+  if (mine) film_add(film, pixel, ps.sum, tp.n_samples);
+  warp_add(stats + ST_PATHS, mine ? ps.s : 0u);
   warp_add(stats + ST_SEGMENTS, n_seg);
   warp_add(stats + ST_SHADE, n_shade);
   if (STATS) {

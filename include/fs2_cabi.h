@@ -194,6 +194,7 @@ typedef struct fs_camera {
 #define FS_TRACE_WAVEFRONT 4  /* use the wavefront pipeline instead of the megakernel */
 #define FS_TRACE_NO_RESOLVE 8 /* skip the mean/gamma resolve (multi-GPU: resolve after the reduce) */
 #define FS_TRACE_ASYNC 16     /* enqueue only: no stream synchronisation before returning */
+#define FS_TRACE_PER_THREAD 32 /* every thread scans its own mesh leaves (no warp-cooperative scan) */
 
 typedef struct fs_stats {
   uint64_t n_paths;    /* camera paths traced since the last reset           */
