@@ -163,6 +163,9 @@ def run_reference(args, rank, world):
     print(json.dumps(line), flush=True)
 
 
+KERNEL_NAME = ["k_trace_mega<stats=0,leaf_bvh=1>"]
+
+
 # --------------------------------------------------------------------------- roofline
 def roofline(ctx_stats, objects, n_pixels, kernel_ms, peaks):
     """Algorithmic bytes / flops per SURVEY.md §8(d) from the stats-build counters of one
@@ -174,10 +177,15 @@ def roofline(ctx_stats, objects, n_pixels, kernel_ms, peaks):
     prim_types = [int(t) for t in objects["type"] if int(t) != 5]
     pb = float(np.mean([per_type_bytes[t] for t in prim_types])) if prim_types else 0.0
     pf = float(np.mean([per_type_flops[t] for t in prim_types])) if prim_types else 0.0
-    nbytes = (32 * s["n_node"] + 56 * s["n_tri"] + pb * s["n_prim"] + 144 * s["n_shade"] +
-              16 * n_pixels)
-    flops = (54 * s["n_node"] + 13 * s["n_tri"] + 23 * s["n_bary"] + pf * s["n_prim"] +
-             120 * s["n_shade"])
+    # our kernel's own algorithmic traffic: octree nodes (32 B), leaf-BVH nodes (128 B), planes
+    # actually tested (16 B), barycentric records actually fetched (48 B), shading, film
+    nbytes = (32 * s["n_node"] + 128 * s["n_lbnode"] + 16 * s["n_tritest"] + 48 * s["n_bary"] +
+              pb * s["n_prim"] + 144 * s["n_shade"] + 16 * n_pixels)
+    flops = (54 * s["n_node"] + 60 * s["n_lbnode"] + 13 * s["n_tritest"] + 23 * s["n_bary"] +
+             pf * s["n_prim"] + 120 * s["n_shade"])
+    # what the reference's loops execute for the same rays (SURVEY.md 8(d) constants)
+    ref_bytes = (32 * s["n_node"] + 56 * s["n_tri"] + pb * s["n_prim"] + 144 * s["n_shade"] +
+                 16 * n_pixels)
     sec = kernel_ms / 1e3
     hbm_peak = peaks.get("hbm_gbs")
     which = "measured"
@@ -187,13 +195,17 @@ def roofline(ctx_stats, objects, n_pixels, kernel_ms, peaks):
     fp32_peak = 148 * 128 * 2 * sm_mhz * 1e6 / 1e12
     return {"bound": "hbm", "achieved": nbytes / sec / 1e9, "peak": hbm_peak, "unit": "GB/s",
             "frac": nbytes / sec / 1e9 / hbm_peak, "traffic": None, "peak_source": which,
-            "kernel": "k_trace_mega", "kernel_ms": kernel_ms,
+            "kernel": KERNEL_NAME[0], "kernel_ms": kernel_ms,
             "algorithmic_bytes": nbytes, "algorithmic_flops": flops,
+            "reference_equivalent_bytes": ref_bytes,
+            "reference_equivalent_gbs": ref_bytes / sec / 1e9,
             "fp32": {"achieved_tflops": flops / sec / 1e12, "peak_tflops": fp32_peak,
                      "frac": flops / sec / 1e12 / fp32_peak},
             "per_segment": {"n_node": s["n_node"] / max(1, s["n_segments"]),
                             "n_tri": s["n_tri"] / max(1, s["n_segments"]),
                             "n_bary": s["n_bary"] / max(1, s["n_segments"]),
+                            "n_lbnode": s["n_lbnode"] / max(1, s["n_segments"]),
+                            "n_tritest": s["n_tritest"] / max(1, s["n_segments"]),
                             "segments_per_path": s["n_segments"] / max(1, s["n_paths"])}}
 
 
@@ -224,7 +236,10 @@ def run_gpu(args, rank, world, local_rank):
     film = multi_gpu.film_tensor(ctx)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     first, n_mine, stride = multi_gpu.shard_samples(SPP, rank, world)
-    flags = abi.FS_TRACE_NO_RESOLVE | abi.FS_TRACE_ASYNC
+    KERNEL_NAME[0] = {"lbvh": "k_trace_mega<0,1> (leaf BVH)", "coop": "k_trace_coop<0>",
+                      "per_thread": "k_trace_mega<0,0> (linear leaves)"}[args.variant]
+    variant = {"lbvh": 0, "coop": abi.FS_TRACE_COOP, "per_thread": abi.FS_TRACE_PER_THREAD}[args.variant]
+    flags = abi.FS_TRACE_NO_RESOLVE | abi.FS_TRACE_ASYNC | variant
 
     def step(seed):
         ctx.reset()
@@ -297,10 +312,11 @@ def run_gpu(args, rank, world, local_rank):
         sctx = fs2_b200.Context(device=local_rank, stats=True)
         sctx.upload(desc)
         sctx.resize(WIDTH, HEIGHT)
-        sctx.trace(cam, 2, seed=SEED)
+        sctx.trace(cam, 2, seed=SEED, flags=variant)
         sst = sctx.stats()
         scale = float(n_mine) / 2.0  # counters grow linearly with samples per pixel
-        for k in ("n_paths", "n_segments", "n_node", "n_tri", "n_bary", "n_prim", "n_shade"):
+        for k in ("n_paths", "n_segments", "n_node", "n_tri", "n_bary", "n_prim", "n_shade",
+                  "n_lbnode", "n_tritest"):
             sst[k] = sst[k] * scale
         sctx.close()
         peaks = {}
@@ -326,6 +342,7 @@ def run_gpu(args, rank, world, local_rank):
                            "scene_bytes": hs.nbytes(), "host_load_build_s": round(load_s, 2),
                            "sharding": "sample indices r, r+N, ... per rank; film reduce to rank 0",
                            "l2": "flushed between steps (256 MiB write)", "seed": SEED,
+                           "variant": args.variant,
                            "time_to_image_ms": total_ms / args.steps,
                            "mrays_per_s": float(segs.item()) / total_ms / 1e3},
                 "clocks": sampler.summary(), "roofline": roof,
@@ -346,6 +363,8 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="fs2")
+    ap.add_argument("--variant", default="lbvh", choices=["lbvh", "coop", "per_thread"],
+                    help="leaf-scan variant of the trace kernel (A/B measurements)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))

@@ -21,6 +21,7 @@ FS_TRACE_WAVEFRONT = 4
 FS_TRACE_NO_RESOLVE = 8
 FS_TRACE_ASYNC = 16
 FS_TRACE_PER_THREAD = 32
+FS_TRACE_COOP = 64
 
 # numpy dtypes of the flattened arrays -------------------------------------------------
 NODE_DT = np.dtype([("bmin", "<f4", 3), ("first", "<u4"), ("bmax", "<f4", 3), ("count", "<u4")])
@@ -68,7 +69,8 @@ class fs_stats(C.Structure):
     _fields_ = [("n_paths", C.c_uint64), ("n_segments", C.c_uint64), ("n_node", C.c_uint64),
                 ("n_tri", C.c_uint64), ("n_bary", C.c_uint64), ("n_prim", C.c_uint64),
                 ("n_shade", C.c_uint64), ("launches", C.c_uint64), ("last_trace_ms", C.c_float),
-                ("last_kernel_ms", C.c_float)]
+                ("last_kernel_ms", C.c_float), ("n_lbnode", C.c_uint64),
+                ("n_tritest", C.c_uint64)]
 
 
 def make_camera(origin=(-5.80, 7.05, -47.06), target=(0.0, 8.94, 0.0), fov_y=45.0,

@@ -16,6 +16,7 @@
 #include <vector>
 
 #include "fs2_kernels.cuh"
+#include "fs2_lbvh_build.h"
 
 using namespace fs2;
 
@@ -40,7 +41,7 @@ struct fs_ctx {
   // scene
   bool have_scene = false;
   DeviceBuf nodes, scene_refs, tri_plane, tri_aux, faces, objects, materials, textures, texels,
-      lut;
+      lut, lb_nodes, lb_leaf, lb_plane, lb_aux, lb_order;
   DScene ds;
   uint32_t n_nodes = 0, n_tris = 0, n_faces = 0, n_materials = 0;
   // film
@@ -276,6 +277,7 @@ int fs_destroy(fs_ctx* ctx) {
   cudaStreamSynchronize(ctx->stream);
   DeviceBuf* all[] = {&ctx->nodes, &ctx->scene_refs, &ctx->tri_plane, &ctx->tri_aux, &ctx->faces,
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
+                      &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
                       &ctx->scratch};
   for (DeviceBuf* b : all) dev_free(b);
@@ -313,8 +315,22 @@ int fs_scene_upload(fs_ctx* ctx, const fs_scene_desc* s) {
   if ((rc = dev_upload(ctx, &ctx->textures, s->textures, (size_t)s->n_textures * sizeof(fs_texture)))) return rc;
   if ((rc = dev_upload(ctx, &ctx->texels, s->texels, (size_t)s->n_texels * 4))) return rc;
   if ((rc = dev_upload(ctx, &ctx->lut, lut4.data(), lut4.size() * 4))) return rc;
+  // leaf BVH over every mesh-tree leaf (fs2_lbvh_build.h); the host vectors must outlive
+  // the asynchronous copies, hence the synchronisation below
+  LbvhHost lb;
+  build_lbvh(s, &lb);
+  if ((rc = dev_upload(ctx, &ctx->lb_nodes, lb.nodes.data(), lb.nodes.size() * sizeof(LbNode)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_leaf, lb.leaf.data(), lb.leaf.size() * sizeof(LbLeaf)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_plane, lb.plane.data(), lb.plane.size() * 4))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_aux, lb.aux.data(), lb.aux.size() * sizeof(fs_tri_aux)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_order, lb.order.data(), lb.order.size() * 4))) return rc;
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   DScene& d = ctx->ds;
+  d.lb_nodes = (const float4*)ctx->lb_nodes.p;
+  d.lb_leaf = (const uint2*)ctx->lb_leaf.p;
+  d.lb_plane = (const float4*)ctx->lb_plane.p;
+  d.lb_aux = (const float4*)ctx->lb_aux.p;
+  d.lb_order = (const uint32_t*)ctx->lb_order.p;
   d.nodes = (const float4*)ctx->nodes.p;
   d.scene_refs = (const uint32_t*)ctx->scene_refs.p;
   d.tri_plane = (const float4*)ctx->tri_plane.p;
@@ -465,14 +481,17 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
   if (n_samples) {
     dim3 grid = pixel_grid(ctx->width, ctx->height);
     const bool per_thread = (flags & FS_TRACE_PER_THREAD) != 0;
-    if (ctx->stats_build && per_thread)
-      k_trace_mega<true><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
-    else if (per_thread)
-      k_trace_mega<false><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
-    else if (ctx->stats_build)
-      k_trace_coop<true><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
-    else
-      k_trace_coop<false><<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats);
+    const bool coop = (flags & FS_TRACE_COOP) != 0;
+    const bool st = ctx->stats_build;
+#define FS2_LAUNCH(K) K<<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats)
+    if (per_thread) {
+      if (st) FS2_LAUNCH((k_trace_mega<true, false>)); else FS2_LAUNCH((k_trace_mega<false, false>));
+    } else if (coop) {
+      if (st) FS2_LAUNCH(k_trace_coop<true>); else FS2_LAUNCH(k_trace_coop<false>);
+    } else {
+      if (st) FS2_LAUNCH((k_trace_mega<true, true>)); else FS2_LAUNCH((k_trace_mega<false, true>));
+    }
+#undef FS2_LAUNCH
     ctx->launches++;
     CUDA_TRY(ctx, cudaGetLastError());
   }
@@ -549,6 +568,8 @@ int fs_get_stats(fs_ctx* ctx, fs_stats* out) {
   out->n_bary = h[ST_BARY];
   out->n_prim = h[ST_PRIM];
   out->n_shade = h[ST_SHADE];
+  out->n_lbnode = h[ST_LBNODE];
+  out->n_tritest = h[ST_TRITEST];
   out->launches = ctx->launches;
   out->last_trace_ms = ctx->last_trace_ms;
   out->last_kernel_ms = ctx->last_kernel_ms;

@@ -24,7 +24,7 @@ struct TraceParams {
 };
 
 // stats slots (device array of unsigned long long)
-enum { ST_PATHS = 0, ST_SEGMENTS, ST_NODE, ST_TRI, ST_BARY, ST_PRIM, ST_SHADE, ST_COUNT };
+enum { ST_PATHS = 0, ST_SEGMENTS, ST_NODE, ST_TRI, ST_BARY, ST_PRIM, ST_SHADE, ST_LBNODE, ST_TRITEST, ST_COUNT };
 
 __device__ __forceinline__ void warp_add(unsigned long long* slot, uint32_t v) {
   v = __reduce_add_sync(0xFFFFFFFFu, v);
@@ -47,7 +47,7 @@ k_first_hit(DScene S, CamBasis cam, int width, int height, float* __restrict__ o
             unsigned long long* __restrict__ stats) {
   int px, py;
   bool valid = pixel_of_thread(width, height, px, py);
-  Counters c = {0, 0, 0, 0};
+  Counters c = {0, 0, 0, 0, 0, 0};
   if (valid) {
     Ray r = camera_ray(cam, (float)px, (float)py, 0.0f, 0.0f);
     Hit h = scene_trace<true>(S, r, c);
@@ -210,14 +210,17 @@ __device__ __forceinline__ void film_add(const Film& film, uint32_t pixel, V3 su
 // Variant A — one thread owns one pixel, walks its own leaves (kept for the ncu comparison
 // and as the FS_TRACE_PER_THREAD path).  A finished path is replaced by the pixel's next
 // sample inside the same loop iteration, so the warp only diverges inside a segment.
-template <bool STATS>
-__global__ void __launch_bounds__(128)
+template <bool STATS, bool LB>
+__global__ void __launch_bounds__(FS2_LB_THREADS)
 k_trace_mega(DScene S, CamBasis cam, Film film, TraceParams tp,
              unsigned long long* __restrict__ stats) {
+  // LB: per-lane stacks of the leaf-BVH walk, one column per thread (conflict-free)
+  __shared__ uint2 lb_stack[LB ? FS2_LB_STACK * FS2_LB_THREADS : 1];
+  uint2* my_stack = lb_stack + (LB ? threadIdx.x : 0);
   int px, py;
   const bool mine = pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0;
   const uint32_t pixel = mine ? (uint32_t)(py * film.width + px) : 0u;
-  Counters c = {0, 0, 0, 0};
+  Counters c = {0, 0, 0, 0, 0, 0};
   uint32_t n_seg = 0, n_shade = 0;
   PathState ps;
   ps.sum = v3(0.f, 0.f, 0.f);
@@ -225,7 +228,7 @@ k_trace_mega(DScene S, CamBasis cam, Film film, TraceParams tp,
   bool alive = mine;
   if (alive) begin_path(cam, tp, pixel, px, py, ps);
   while (alive) {
-    Hit h = scene_trace<STATS>(S, ps.ray, c);
+    Hit h = scene_trace<STATS, LB>(S, ps.ray, c, my_stack);
     n_seg++;
     alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, h, n_shade);
   }
@@ -238,6 +241,8 @@ k_trace_mega(DScene S, CamBasis cam, Film film, TraceParams tp,
     warp_add(stats + ST_TRI, c.n_tri);
     warp_add(stats + ST_BARY, c.n_bary);
     warp_add(stats + ST_PRIM, c.n_prim);
+    warp_add(stats + ST_LBNODE, c.n_lbnode);
+    warp_add(stats + ST_TRITEST, c.n_tritest);
   }
 }
 
@@ -251,7 +256,7 @@ k_trace_coop(DScene S, CamBasis cam, Film film, TraceParams tp,
   int px, py;
   const bool mine = pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0;
   const uint32_t pixel = mine ? (uint32_t)(py * film.width + px) : 0u;
-  Counters c = {0, 0, 0, 0};
+  Counters c = {0, 0, 0, 0, 0, 0};
   uint32_t n_seg = 0, n_shade = 0;
   PathState ps;
   ps.sum = v3(0.f, 0.f, 0.f);

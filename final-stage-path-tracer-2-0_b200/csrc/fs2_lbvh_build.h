@@ -1,0 +1,324 @@
+// fs2_lbvh_build.h — builds the per-leaf 4-wide BVH ("leaf BVH") at scene upload.
+//
+// The reference's mesh octree stops at depth 4 (source/mesh.cpp:15-16,39-44), so its leaves
+// hold hundreds to thousands of face references that MeshBvhNode::Trace scans linearly
+// (source/mesh.cpp:89-110).  That loop is a pure function of the leaf: the accepted triangle
+// with the smallest parameter below the incoming best, first in leaf order on ties.  This
+// builder re-orders each leaf's packed records along a Morton curve and stacks an implicit
+// 4-ary tree of conservative boxes on top, so a ray only runs the reference's triangle test
+// on the groups of four it can actually touch.  Device-layout detail, not part of the ABI.
+#pragma once
+#include <math.h>
+#include <stdint.h>
+#include <string.h>
+
+#include <algorithm>
+#include <atomic>
+#include <thread>
+#include <vector>
+
+#include "../../include/fs2_cabi.h"
+
+namespace fs2 {
+
+// Leaves with fewer triangles than this are scanned directly (one node, no tree).
+#define FS2_LBVH_MAX_LEVELS 7  // 4^(7+1) = 65 536 triangles per octree leaf
+
+// 128-byte node: boxes of its 4 children as SoA, then the link word.
+struct LbNode {
+  float lox[4], loy[4], loz[4], hix[4], hiy[4], hiz[4];
+  uint32_t child;  // inner: index of child node 0 (children contiguous); quad level: first triangle
+  uint32_t kind;   // 0 = children are nodes, 1 = children are groups of <= 4 triangles
+  uint32_t count;  // quad level: number of triangles under this node (<= 16); inner: children
+  uint32_t pad;
+  uint32_t spare[4];
+};
+static_assert(sizeof(LbNode) == 128, "LbNode must be 128 bytes");
+
+struct LbLeaf {
+  uint32_t root;   // LbNode index of the leaf's root, 0xFFFFFFFF = no tree (scan first/count)
+  uint32_t first;  // first record in the permuted arrays (== fs_node.first)
+};
+
+struct LbvhHost {
+  std::vector<float> plane;        // permuted copy of tri_plane (4 floats per record)
+  std::vector<fs_tri_aux> aux;     // permuted copy of tri_aux
+  std::vector<uint32_t> order;     // permuted index -> original packed index
+  std::vector<LbNode> nodes;
+  std::vector<LbLeaf> leaf;        // one per octree node
+  std::vector<uint8_t> mesh_leaf;  // 1 for nodes that are leaves of a mesh tree
+};
+
+namespace lbvh_detail {
+
+struct Box3 {
+  float lo[3], hi[3];
+  void reset() {
+    lo[0] = lo[1] = lo[2] = INFINITY;
+    hi[0] = hi[1] = hi[2] = -INFINITY;
+  }
+  void add(const float p[3]) {
+    for (int k = 0; k < 3; k++) {
+      if (p[k] < lo[k]) lo[k] = p[k];
+      if (p[k] > hi[k]) hi[k] = p[k];
+    }
+  }
+  void add(const Box3& b) {
+    for (int k = 0; k < 3; k++) {
+      if (b.lo[k] < lo[k]) lo[k] = b.lo[k];
+      if (b.hi[k] > hi[k]) hi[k] = b.hi[k];
+    }
+  }
+};
+
+// The three vertices of a packed record.  fs_tri_aux keeps p1 and the two kept components
+// of the edges (include/fs2_pack.h); the dropped component of p2/p3 is recovered from the
+// face plane, whose dominant axis is the dropped one (|n_drop| >= |n|/sqrt(3)).
+inline void record_vertices(const float pl[4], const fs_tri_aux& a, float v[4][3]) {
+  int drop = (int)(a.face >> 30);
+  int ia = (drop == 0) ? 1 : 0, ib = (drop == 2) ? 1 : 2;
+  for (int k = 0; k < 3; k++) v[0][k] = v[1][k] = v[2][k] = v[3][k] = a.p1[k];
+  v[1][ia] = a.p1[ia] + a.v0a;
+  v[1][ib] = a.p1[ib] + a.v0b;
+  v[2][ia] = a.p1[ia] + a.v1a;
+  v[2][ib] = a.p1[ib] + a.v1b;
+  double nd = pl[drop];
+  if (nd != 0.0) {
+    // v[3] = p1 moved onto the stored plane: an accepted hit lies on the plane, so its dropped
+    // coordinate is a blend of the plane heights at the three projected corners
+    for (int j = 1; j < 4; j++)
+      v[j][drop] = (float)(-((double)pl[3] + (double)pl[ia] * v[j][ia] + (double)pl[ib] * v[j][ib]) / nd);
+  }
+}
+
+// Conservative box of one record: vertex hull padded by 64 ulp of the largest coordinate
+// plus 0.1 % of the extent (rounding of the reference's hit point and barycentrics is a few
+// ulp of the coordinates; the plane-recovered component adds a few more).
+inline Box3 record_box(const float pl[4], const fs_tri_aux& a) {
+  float v[4][3];
+  record_vertices(pl, a, v);
+  Box3 b;
+  b.reset();
+  for (int j = 0; j < 4; j++) b.add(v[j]);
+  float m = 0.f, ext = 0.f;
+  for (int k = 0; k < 3; k++) {
+    m = fmaxf(m, fmaxf(fabsf(b.lo[k]), fabsf(b.hi[k])));
+    ext = fmaxf(ext, b.hi[k] - b.lo[k]);
+  }
+  float pad = m * (64.0f * 1.1920929e-7f) + ext * 1.0e-3f + 1.0e-30f;
+  if (!(pad == pad) || isinf(pad)) {  // degenerate record: make the box cover everything
+    for (int k = 0; k < 3; k++) {
+      b.lo[k] = -INFINITY;
+      b.hi[k] = INFINITY;
+    }
+    return b;
+  }
+  for (int k = 0; k < 3; k++) {
+    b.lo[k] -= pad;
+    b.hi[k] += pad;
+  }
+  return b;
+}
+
+inline uint32_t spread3(uint32_t x) {
+  x &= 0x3FFu;
+  x = (x | (x << 16)) & 0x030000FFu;
+  x = (x | (x << 8)) & 0x0300F00Fu;
+  x = (x | (x << 4)) & 0x030C30C3u;
+  x = (x | (x << 2)) & 0x09249249u;
+  return x;
+}
+
+}  // namespace lbvh_detail
+
+namespace lbvh_detail {
+
+struct LeafJob {
+  uint32_t node;        // octree node index
+  uint32_t first, count;
+  uint32_t node_base;   // first LbNode of this leaf (root)
+  uint32_t n_nodes;
+};
+
+// Number of LbNodes of a leaf with n records: levels of ceil-div by 4 down to one node.
+inline uint32_t leaf_node_count(uint32_t n) {
+  uint32_t q = (n + 3) / 4, total = 0;
+  uint32_t m = q;
+  do {
+    m = (m + 3) / 4;
+    total += m;
+  } while (m > 1);
+  return total;
+}
+
+// Builds one leaf: permutes records [first, first+count) and writes its nodes, root first,
+// then level by level towards the quad level (children of a node are contiguous).
+inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out) {
+  const uint32_t n = job.count, first = job.first;
+  std::vector<Box3> boxes(n);
+  std::vector<uint64_t> keys(n);
+  Box3 cb;
+  cb.reset();
+  std::vector<float> cen(3 * (size_t)n);
+  for (uint32_t i = 0; i < n; i++) {
+    const float* pl = s->tri_plane + 4 * (size_t)(first + i);
+    boxes[i] = record_box(pl, s->tri_aux[first + i]);
+    for (int k = 0; k < 3; k++) {
+      float c = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
+      if (!(c == c) || isinf(c)) c = 0.f;
+      cen[3 * (size_t)i + k] = c;
+    }
+    cb.add(&cen[3 * (size_t)i]);
+  }
+  float scale[3];
+  for (int k = 0; k < 3; k++) {
+    float e = cb.hi[k] - cb.lo[k];
+    scale[k] = e > 0.f ? 1023.0f / e : 0.f;
+  }
+  for (uint32_t i = 0; i < n; i++) {
+    uint32_t q[3];
+    for (int k = 0; k < 3; k++) {
+      float f = (cen[3 * (size_t)i + k] - cb.lo[k]) * scale[k];
+      q[k] = (uint32_t)fminf(fmaxf(f, 0.f), 1023.f);
+    }
+    uint32_t code = spread3(q[0]) | (spread3(q[1]) << 1) | (spread3(q[2]) << 2);
+    keys[i] = ((uint64_t)code << 32) | i;
+  }
+  std::sort(keys.begin(), keys.end());
+  std::vector<Box3> cur(n);
+  for (uint32_t i = 0; i < n; i++) {
+    uint32_t src = (uint32_t)(keys[i] & 0xFFFFFFFFu);
+    memcpy(&out->plane[4 * (size_t)(first + i)], s->tri_plane + 4 * (size_t)(first + src), 16);
+    out->aux[first + i] = s->tri_aux[first + src];
+    out->order[first + i] = first + src;
+    cur[i] = boxes[src];
+  }
+  // level sizes, bottom (quad level) to top
+  uint32_t q = (n + 3) / 4;
+  std::vector<Box3> item(q);  // boxes of the items the next level groups: quads first
+  for (uint32_t g = 0; g < q; g++) {
+    item[g].reset();
+    for (uint32_t j = 4 * g; j < 4 * g + 4 && j < n; j++) item[g].add(cur[j]);
+  }
+  std::vector<uint32_t> sizes;
+  for (uint32_t m = q;;) {
+    m = (m + 3) / 4;
+    sizes.push_back(m);
+    if (m <= 1) break;
+  }
+  // offsets: root level first
+  const int L = (int)sizes.size();
+  std::vector<uint32_t> base(L);
+  uint32_t acc = job.node_base;
+  for (int l = L - 1; l >= 0; l--) {
+    base[l] = acc;
+    acc += sizes[l];
+  }
+  for (int l = 0; l < L; l++) {
+    std::vector<Box3> next(sizes[l]);
+    const uint32_t n_items = (uint32_t)item.size();
+    for (uint32_t i = 0; i < sizes[l]; i++) {
+      LbNode& nd = out->nodes[base[l] + i];
+      memset(&nd, 0, sizeof nd);
+      next[i].reset();
+      uint32_t kids = 0;
+      for (uint32_t c = 0; c < 4; c++) {
+        uint32_t j = 4 * i + c;
+        if (j < n_items) {
+          nd.lox[c] = item[j].lo[0];
+          nd.loy[c] = item[j].lo[1];
+          nd.loz[c] = item[j].lo[2];
+          nd.hix[c] = item[j].hi[0];
+          nd.hiy[c] = item[j].hi[1];
+          nd.hiz[c] = item[j].hi[2];
+          next[i].add(item[j]);
+          kids++;
+        } else {  // empty slot: never hit
+          nd.lox[c] = nd.loy[c] = nd.loz[c] = INFINITY;
+          nd.hix[c] = nd.hiy[c] = nd.hiz[c] = INFINITY;
+        }
+      }
+      if (l == 0) {
+        nd.kind = 1;
+        nd.child = first + 16 * i;
+        uint32_t rem = n - 16 * i;
+        nd.count = rem < 16 ? rem : 16;
+      } else {
+        nd.kind = 0;
+        nd.child = base[l - 1] + 4 * i;
+        nd.count = kids;
+      }
+    }
+    item.swap(next);
+  }
+}
+
+}  // namespace lbvh_detail
+
+// Builds the leaf BVHs of every mesh-tree leaf of `s`.  min_leaf: leaves with fewer records
+// keep root = 0xFFFFFFFF (scanned linearly).  Leaves beyond the level cap stay linear too.
+inline void build_lbvh(const fs_scene_desc* s, LbvhHost* out, uint32_t min_leaf = 9,
+                       unsigned threads = 0) {
+  using namespace lbvh_detail;
+  out->plane.assign(s->tri_plane, s->tri_plane + 4 * (size_t)s->n_tris);
+  out->aux.assign(s->tri_aux, s->tri_aux + s->n_tris);
+  out->order.resize(s->n_tris);
+  for (uint32_t i = 0; i < s->n_tris; i++) out->order[i] = i;
+  out->leaf.assign(s->n_nodes, LbLeaf{0xFFFFFFFFu, 0});
+  out->mesh_leaf.assign(s->n_nodes, 0);
+  // enumerate mesh-tree leaves
+  std::vector<LeafJob> jobs;
+  std::vector<uint32_t> stack;
+  std::vector<uint8_t> seen(s->n_nodes, 0);
+  uint32_t total_nodes = 0;
+  for (uint32_t o = 0; o < s->n_objects; o++) {
+    const fs_object& ob = s->objects[o];
+    if (ob.type != FS_OBJ_MESH || ob.u[0] == 0xFFFFFFFFu) continue;
+    stack.push_back(ob.u[0]);
+    while (!stack.empty()) {
+      uint32_t ni = stack.back();
+      stack.pop_back();
+      if (ni >= s->n_nodes || seen[ni]) continue;
+      seen[ni] = 1;
+      const fs_node& nd = s->nodes[ni];
+      if (nd.count == FS_NODE_INTERNAL) {
+        for (uint32_t c = 0; c < 8; c++) stack.push_back(nd.first + c);
+        continue;
+      }
+      out->leaf[ni].first = nd.first;
+      out->mesh_leaf[ni] = 1;
+      if ((uint64_t)nd.first + nd.count > s->n_tris) continue;  // malformed: stay linear
+      if (nd.count < min_leaf || nd.count > (1u << (2 * (FS2_LBVH_MAX_LEVELS + 1)))) continue;
+      LeafJob j;
+      j.node = ni;
+      j.first = nd.first;
+      j.count = nd.count;
+      j.n_nodes = leaf_node_count(nd.count);
+      j.node_base = total_nodes;
+      total_nodes += j.n_nodes;
+      jobs.push_back(j);
+    }
+  }
+  out->nodes.resize(total_nodes ? total_nodes : 1);
+  for (const LeafJob& j : jobs) out->leaf[j.node].root = j.node_base;
+  if (threads == 0) threads = std::thread::hardware_concurrency();
+  if (threads == 0) threads = 1;
+  if (threads > 32) threads = 32;
+  std::atomic<size_t> next(0);
+  auto work = [&]() {
+    for (;;) {
+      size_t i = next.fetch_add(1);
+      if (i >= jobs.size()) break;
+      build_leaf(s, jobs[i], out);
+    }
+  };
+  if (threads <= 1 || jobs.size() < 8) {
+    work();
+  } else {
+    std::vector<std::thread> pool;
+    for (unsigned t = 0; t < threads; t++) pool.emplace_back(work);
+    for (auto& t : pool) t.join();
+  }
+}
+
+}  // namespace fs2

@@ -24,6 +24,12 @@ struct DScene {
   const fs_texture* textures;
   const float* texels;
   const float4* lut;        // xyz + pad
+  // leaf BVH (fs2_lbvh_build.h): permuted triangle records + 128-byte 4-wide nodes
+  const float4* lb_nodes;   // 8 x float4 per LbNode
+  const uint2* lb_leaf;     // per octree node: (root LbNode or 0xFFFFFFFF, first record)
+  const float4* lb_plane;
+  const float4* lb_aux;
+  const uint32_t* lb_order; // permuted index -> original packed index
   uint32_t n_objects;
   uint32_t n_lut;
   uint32_t sky_material;
@@ -31,7 +37,8 @@ struct DScene {
 };
 
 struct Counters {
-  uint32_t n_node, n_tri, n_bary, n_prim;
+  uint32_t n_node, n_tri, n_bary, n_prim;  // reference-equivalent work
+  uint32_t n_lbnode, n_tritest;            // leaf-BVH kernel's own work: nodes visited, planes tested
 };
 
 // Running nearest hit.  prim: packed-triangle index for meshes, face plane for cuboids.
@@ -200,6 +207,10 @@ __device__ __forceinline__ bool mesh_leaf(const DScene& S, uint32_t first, uint3
   return improved;
 }
 
+}  // namespace fs2
+#include "fs2_lbvh.cuh"
+namespace fs2 {
+
 // ------------------------------------------------------------------ octree walker
 // Frame of one internal node whose children are being visited (bvh.h:154-231).
 struct Frame {
@@ -234,7 +245,7 @@ __device__ __forceinline__ float split_param(float start_c, float dir_c, float c
   return (t >= 0.0f && t <= 1.0f) ? t : 2.0f;
 }
 
-// Walks the octree under `root`.  leaf(first, count, best) returns true when it improved
+// Walks the octree under `root`.  leaf(node, first, count, best) returns true when it improved
 // `best`; the walker only needs best.param (culling, early exit).  Returns true when any
 // leaf improved the record, i.e. the reference's node->Trace() result.
 template <int MAXD, bool STATS, class Leaf>
@@ -255,7 +266,7 @@ __device__ __forceinline__ bool walk_octree(const DScene& S, uint32_t root, cons
       if (!ray_box(n.mn, n.mx, r, nparam, entry, inside) || nparam > best.param) {
         ret = false;
       } else if (n.count != FS_NODE_INTERNAL) {
-        ret = n.count ? leaf(n.first, n.count, best) : false;
+        ret = n.count ? leaf(cur, n.first, n.count, best) : false;
       } else if (sp < MAXD) {
         // bvh.h:160-186 — the zero-length ray has entry == start as well
         V3 cen = (n.mn + n.mx) * 0.5f;
@@ -365,16 +376,24 @@ __device__ __forceinline__ bool sphere_test(V3 centre, float radius, const Ray& 
   return true;
 }
 
-template <bool STATS>
+// Per-segment context of the leaf-BVH variant (LB = true); unused otherwise.
+struct LbCtx {
+  LbRay q;
+  uint2* stack;  // this lane's column of the shared-memory stack
+};
+
+template <bool STATS, bool LB = false>
 __device__ __forceinline__ bool object_trace(const DScene& S, uint32_t oi, const Ray& r, Hit& h,
-                                             Counters& c) {
+                                             Counters& c, const LbCtx* lb = nullptr) {
   float4 w0 = obj_word(S, oi, 0);
   uint32_t type = __float_as_uint(w0.x);
   if (type == FS_OBJ_MESH) {
     uint32_t root = __float_as_uint(w0.z);
     if (root == 0xFFFFFFFFu) return false;
     return walk_octree<FS2_MESH_STACK, STATS>(
-        S, root, r, h, c, [&](uint32_t first, uint32_t count, Hit& best) {
+        S, root, r, h, c, [&](uint32_t node, uint32_t first, uint32_t count, Hit& best) {
+          if (LB && !r.zero_length)
+            return lbvh_leaf<STATS>(S, node, first, count, r, lb->q, oi, best, c, lb->stack);
           return mesh_leaf<STATS>(S, first, count, r, oi, best, c);
         });
   }
@@ -462,20 +481,28 @@ __device__ __forceinline__ bool object_trace(const DScene& S, uint32_t oi, const
 
 // reference source/scene.cpp:227-237 (the normal flip of :238-247 is applied when the
 // surface record is rebuilt).
-template <bool STATS>
-__device__ __forceinline__ Hit scene_trace(const DScene& S, const Ray& r, Counters& c) {
+template <bool STATS, bool LB = false>
+__device__ __forceinline__ Hit scene_trace(const DScene& S, const Ray& r, Counters& c,
+                                           uint2* lb_stack = nullptr) {
   Hit best = no_hit();
+  LbCtx lbc;
+  if (LB) {
+    lbc.q = make_lbray(r);
+    lbc.stack = lb_stack;
+  }
+  const LbCtx* lb = LB ? &lbc : nullptr;
   if (S.scene_root < 0) {
-    for (uint32_t i = 0; i < S.n_objects; i++) object_trace<STATS>(S, i, r, best, c);
+    for (uint32_t i = 0; i < S.n_objects; i++) object_trace<STATS, LB>(S, i, r, best, c, lb);
   } else {
     walk_octree<FS2_SCENE_STACK, STATS>(
-        S, (uint32_t)S.scene_root, r, best, c, [&](uint32_t first, uint32_t count, Hit& glob) {
+        S, (uint32_t)S.scene_root, r, best, c,
+        [&](uint32_t, uint32_t first, uint32_t count, Hit& glob) {
           // scene.cpp:84-99: one temporary record (param 2.0) shared by the leaf's objects
           bool improved = false;
           Hit temp = no_hit();
           for (uint32_t i = 0; i < count; i++) {
             uint32_t oi = __ldg(S.scene_refs + first + i);
-            if (object_trace<STATS>(S, oi, r, temp, c) && temp.param < glob.param) {
+            if (object_trace<STATS, LB>(S, oi, r, temp, c, lb) && temp.param < glob.param) {
               glob = temp;
               improved = true;
             }

@@ -194,7 +194,9 @@ typedef struct fs_camera {
 #define FS_TRACE_WAVEFRONT 4  /* use the wavefront pipeline instead of the megakernel */
 #define FS_TRACE_NO_RESOLVE 8 /* skip the mean/gamma resolve (multi-GPU: resolve after the reduce) */
 #define FS_TRACE_ASYNC 16     /* enqueue only: no stream synchronisation before returning */
-#define FS_TRACE_PER_THREAD 32 /* every thread scans its own mesh leaves (no warp-cooperative scan) */
+#define FS_TRACE_PER_THREAD 32 /* every thread scans its own mesh leaves linearly, in reference order */
+#define FS_TRACE_COOP 64       /* linear leaf scans done by the whole warp, 32 triangles per step */
+/* default (neither): every thread walks the per-leaf 4-wide BVH built by fs_scene_upload */
 
 typedef struct fs_stats {
   uint64_t n_paths;    /* camera paths traced since the last reset           */
@@ -207,6 +209,10 @@ typedef struct fs_stats {
   uint64_t launches;   /* kernels launched by this context since the last reset */
   float last_trace_ms;  /* device time of the last fs_trace, all its kernels (CUDA events) */
   float last_kernel_ms; /* device time of the path-tracing kernel(s) alone in that call   */
+  /* n_node/n_tri/n_bary above count reference-equivalent work (what the reference's loops
+   * execute for the same rays).  The default kernel's own work (stats build only): */
+  uint64_t n_lbnode;  /* leaf-BVH nodes visited (128 B each)                               */
+  uint64_t n_tritest; /* triangle plane tests actually executed                            */
 } fs_stats;
 
 typedef struct fs_ctx fs_ctx;

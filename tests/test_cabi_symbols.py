@@ -29,7 +29,7 @@ def test_every_declared_symbol_is_exported():
 
 def test_struct_sizes_match_header():
     assert C.sizeof(abi.fs_camera) == 48
-    assert C.sizeof(abi.fs_stats) == 72
+    assert C.sizeof(abi.fs_stats) == 88
     assert C.sizeof(abi.fs_scene_desc) == 56 + 10 * 8
     assert abi.NODE_DT.itemsize == 32 and abi.OBJECT_DT.itemsize == 144
 

@@ -97,25 +97,46 @@ def test_aux_buffers_match_oracle_without_jitter(ctx):
     assert (f["depth"][hit].view(np.uint32) == o["range"][hit].view(np.uint32)).all()
 
 
-@pytest.mark.parametrize("name", ["mesh_tiny", "many303", "grid_tiny", "api"])
-def test_cooperative_and_per_thread_kernels_agree_bit_for_bit(ctx, name):
-    """The warp-cooperative leaf scan must reproduce the sequential leaf loop exactly: same
-    seeds -> identical hits -> identical films and identical work counters."""
+def _variants_agree(ctx, scene, cam, w, h, spp):
+    """default (leaf-BVH walk), warp-cooperative linear scan and per-thread linear scan (the
+    reference's loop order) must produce identical hits: same seeds -> identical films, aux
+    buffers, ids and reference-equivalent work counters."""
     import fs2_b200
-    g = golden(name)
-    w, h = 80, 48
-    ctx.upload(g.scene)
+    ctx.upload(scene)
     ctx.resize(w, h)
     out = []
-    for flags in (0, fs2_b200.FS_TRACE_PER_THREAD):
+    for flags in (0, fs2_b200.FS_TRACE_COOP, fs2_b200.FS_TRACE_PER_THREAD):
         ctx.reset()
         ctx.reset_stats()
-        ctx.trace(g.cam, 6, seed=11, flags=flags)
+        ctx.trace(cam, spp, seed=11, flags=flags)
         f = ctx.read_film(aux=True)
         out.append((f, ctx.stats()))
-    (fa, sa), (fb, sb) = out
-    assert (fa["mean"].view(np.uint32) == fb["mean"].view(np.uint32)).all()
-    assert (fa["normal"].view(np.uint32) == fb["normal"].view(np.uint32)).all()
-    assert (fa["mat_id"] == fb["mat_id"]).all()
+    (fl, sl), (fa, sa), (fb, sb) = out
+    for f in (fl, fa):
+        assert (f["mean"].view(np.uint32) == fb["mean"].view(np.uint32)).all()
+        assert (f["normal"].view(np.uint32) == fb["normal"].view(np.uint32)).all()
+        assert (f["depth"].view(np.uint32) == fb["depth"].view(np.uint32)).all()
+        assert (f["mat_id"] == fb["mat_id"]).all()
     for k in ("n_paths", "n_segments", "n_node", "n_tri", "n_bary", "n_prim", "n_shade"):
         assert sa[k] == sb[k], k
+        if k != "n_bary":  # the BVH walk does not visit every triangle of a leaf
+            assert sl[k] == sb[k], k
+    return sl
+
+
+@pytest.mark.parametrize("name", ["mesh_tiny", "many303", "grid_tiny", "api", "glass_small"])
+def test_kernel_variants_agree_bit_for_bit(ctx, name):
+    g = golden(name)
+    _variants_agree(ctx, g.scene, g.cam, 80, 48, 6)
+
+
+@pytest.mark.parametrize("name,w,h,spp", [("mesh_small", 160, 90, 4), ("mesh100k", 240, 135, 2),
+                                          ("grid_small", 160, 90, 2)])
+def test_kernel_variants_agree_on_generated_meshes(ctx, name, w, h, spp, tmp_path_factory):
+    """Fat leaves (hundreds to thousands of triangles): the leaf BVH must not lose a hit."""
+    import gen_scenes
+    from fs2_b200 import host
+    d = str(tmp_path_factory.mktemp("gen"))
+    hs = host.HostScene(gen_scenes.generate(d, [name])[name])
+    st = _variants_agree(ctx, hs.desc(), hs.camera(), w, h, spp)
+    assert st["n_tritest"] < st["n_tri"]  # and it must actually skip work

@@ -1,0 +1,43 @@
+"""Leaf-BVH builder + walk (csrc/fs2_lbvh_build.h, host restatement of csrc/fs2_lbvh.cuh in
+tests/cpp/lbvh_check.cpp) against the reference's linear leaf loop (source/mesh.cpp:89-110)
+on the CPU: identical (parameter bits, record, u, v) for random, axis-parallel and
+vertex/edge-grazing segments, with and without an incoming best."""
+import os
+import subprocess
+
+import pytest
+
+import fs2_b200  # noqa: F401
+import gen_scenes
+from fs2_b200 import host
+from refdata import golden
+
+REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+@pytest.fixture(scope="module")
+def checker(tmp_path_factory):
+    exe = str(tmp_path_factory.mktemp("lbvh") / "lbvh_check")
+    subprocess.run(["g++", "-std=c++17", "-O2", "-ffp-contract=off", "-I" + os.path.join(REPO, "include"),
+                    "-I" + os.path.join(REPO, "final-stage-path-tracer-2-0_b200", "csrc"),
+                    os.path.join(REPO, "tests", "cpp", "lbvh_check.cpp"), "-o", exe, "-lpthread"],
+                   check=True)
+    return exe
+
+
+@pytest.mark.parametrize("name", ["mesh_tiny", "grid_tiny"])
+def test_leaf_bvh_equals_linear_scan_golden_scenes(checker, name, tmp_path):
+    blob = str(tmp_path / "s.fs2")
+    golden(name).scene.save(blob)
+    r = subprocess.run([checker, blob, "20000", "5"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert r.stdout.startswith("ok")
+
+
+def test_leaf_bvh_equals_linear_scan_fat_leaves(checker, tmp_path):
+    hs = host.HostScene(gen_scenes.generate(str(tmp_path), ["mesh_small"])["mesh_small"])
+    blob = str(tmp_path / "s.fs2")
+    hs.save_blob(blob)
+    r = subprocess.run([checker, blob, "30000", "9"], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    assert " 0 mismatches" in r.stdout
