@@ -258,6 +258,12 @@ int fs_create(fs_ctx** out, int device, int flags) {
     if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->ev1);
     if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->evk0);
     if (e1 == cudaSuccess) e1 = cudaEventCreate(&ctx->evk1);
+    if (e1 == cudaSuccess)
+      e1 = cudaFuncSetAttribute(k_trace_phase<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                FS2_PH_SMEM_BYTES);
+    if (e1 == cudaSuccess)
+      e1 = cudaFuncSetAttribute(k_trace_phase<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                FS2_PH_SMEM_BYTES);
     if (e1 == cudaSuccess) e1 = cudaMalloc(&ctx->d_stats, ST_COUNT * sizeof(unsigned long long));
     if (e1 == cudaSuccess)
       e1 = cudaMemset(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long));
@@ -488,8 +494,15 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
       if (st) FS2_LAUNCH((k_trace_mega<true, false>)); else FS2_LAUNCH((k_trace_mega<false, false>));
     } else if (coop) {
       if (st) FS2_LAUNCH(k_trace_coop<true>); else FS2_LAUNCH(k_trace_coop<false>);
-    } else {
+    } else if (flags & FS_TRACE_LBVH_LANE) {
       if (st) FS2_LAUNCH((k_trace_mega<true, true>)); else FS2_LAUNCH((k_trace_mega<false, true>));
+    } else {
+      if (st)
+        k_trace_phase<true><<<grid, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(
+            ctx->ds, cb, film, tp, ctx->d_stats);
+      else
+        k_trace_phase<false><<<grid, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(
+            ctx->ds, cb, film, tp, ctx->d_stats);
     }
 #undef FS2_LAUNCH
     ctx->launches++;

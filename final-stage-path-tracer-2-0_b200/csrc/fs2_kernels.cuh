@@ -7,6 +7,7 @@
 #pragma once
 #include "fs2_coop.cuh"
 #include "fs2_shade.cuh"
+#include "fs2_phase.cuh"
 
 namespace fs2 {
 
@@ -294,6 +295,94 @@ k_trace_coop(DScene S, CamBasis cam, Film film, TraceParams tp,
     warp_add(stats + ST_TRI, c.n_tri);
     warp_add(stats + ST_BARY, c.n_bary);
     warp_add(stats + ST_PRIM, c.n_prim);
+  }
+}
+
+// Variant C (default) — warp-synchronous phase machine (fs2_phase.cuh) over the leaf BVH.
+// Same per-pixel ownership and path regeneration as the other variants.
+#define FS2_PHASE(STATE, MAXREP, CALL)                                   \
+  _Pragma("unroll 1") for (int rep_ = 0; rep_ < (MAXREP); ++rep_) {      \
+    unsigned m_ = __ballot_sync(0xFFFFFFFFu, w.st == (STATE));           \
+    if (!m_ || (rep_ && __popc(m_) < FS2_PH_REPEAT_MIN)) break;          \
+    if (w.st == (STATE)) {                                               \
+      CALL;                                                              \
+    }                                                                    \
+  }
+
+template <bool STATS>
+__global__ void __launch_bounds__(FS2_PH_THREADS, 4)
+k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
+              unsigned long long* __restrict__ stats) {
+  extern __shared__ uint32_t ph_smem[];
+  PhSmem sm;
+  sm.col = ph_smem + threadIdx.x;
+  int px, py;
+  const bool mine = pixel_of_thread(film.width, film.height, px, py) && tp.n_samples > 0;
+  const uint32_t pixel = mine ? (uint32_t)(py * film.width + px) : 0u;
+  Counters c = {0, 0, 0, 0, 0, 0};
+  uint32_t n_seg = 0, n_shade = 0;
+  PathState ps;
+  ps.sum = v3(0.f, 0.f, 0.f);
+  ps.s = 0;
+  ps.ray = make_ray(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f));
+  PhLane w;
+  w.st = PH_IDLE;
+  w.rec = no_hit();
+  w.glob = no_hit();
+  w.obj_i = w.cur_obj = w.sleaf_first = w.sleaf_count = w.sleaf_i = w.cur = 0;
+  w.msp = w.ssp = 0;
+  w.flags = 0;
+  w.lb_cur = 0;
+  w.lb_sp = 0;
+  w.bt = w.bu = w.bv = 0.f;
+  w.border = w.qbase = w.qcount = w.qmask = 0;
+  LbRay q = make_lbray(ps.ray);
+  if (mine) {
+    begin_path(cam, tp, pixel, px, py, ps);
+    w.st = PH_SEG_START;
+  }
+  for (;;) {
+    if (w.st == PH_SEG_START) {  // scene.cpp:227-237
+      w.rec = no_hit();
+      w.flags = 0;
+      w.ssp = 0;
+      q = make_lbray(ps.ray);
+      if (S.scene_root < 0) {
+        w.obj_i = 0;
+        w.st = PH_OBJ;
+      } else {
+        w.cur = (uint32_t)S.scene_root;
+        w.st = PH_ENTER;
+      }
+    }
+    FS2_PHASE(PH_OBJ, 3, ph_object<STATS>(S, w, ps.ray, c))
+    FS2_PHASE(PH_ENTER, 2, ph_enter<STATS>(S, w, ps.ray, sm, c))
+    FS2_PHASE(PH_LB_NODE, 2, ph_lb_node<STATS>(S, w, ps.ray, q, sm, c))
+    FS2_PHASE(PH_LB_TRIS, 2, ph_lb_tris<STATS>(S, w, ps.ray, sm, c))
+    FS2_PHASE(PH_RETURN, 4, ph_return(S, w, ps.ray, sm))
+    unsigned m_shade = __ballot_sync(0xFFFFFFFFu, w.st == PH_SHADE);
+    unsigned m_busy = __ballot_sync(0xFFFFFFFFu, w.st != PH_SHADE && w.st != PH_IDLE);
+    if (m_shade && (__popc(m_shade) >= FS2_PH_SHADE_BATCH || !m_busy)) {
+      if (w.st == PH_SHADE) {
+        n_seg++;
+        bool alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, w.rec, n_shade);
+        w.st = alive ? PH_SEG_START : PH_IDLE;
+      }
+    } else if (!m_busy) {
+      break;  // every lane is idle
+    }
+  }
+  if (mine) film_add(film, pixel, ps.sum, tp.n_samples);
+  warp_add(stats + ST_PATHS, mine ? ps.s : 0u);
+  warp_add(stats + ST_SEGMENTS, n_seg);
+  warp_add(stats + ST_SHADE, n_shade);
+  if (STATS) {
+    warp_add(stats + ST_NODE, c.n_node);
+    warp_add(stats + ST_TRI, c.n_tri);
+    warp_add(stats + ST_BARY, c.n_bary);
+    warp_add(stats + ST_PRIM, c.n_prim);
+    warp_add(stats + ST_LBNODE, c.n_lbnode);
+    warp_add(stats + ST_TRITEST, c.n_tritest);
   }
 }
 

@@ -1,0 +1,395 @@
+// fs2_phase.cuh — warp-synchronous phase machine for the path-tracing megakernel.
+//
+// Why: ncu on the per-lane walkers (k_trace_mega) shows 2.2-2.8 active threads per executed
+// warp instruction: nested data-dependent loops (octree walk -> leaf BVH walk -> triangle
+// loop) let the 32 lanes of a warp drift into different loop nests and the hardware runs
+// them one after the other.  Here every lane keeps an explicit state and the warp executes
+// one *phase* at a time — all lanes that are in state X run step X together, then the warp
+// re-converges and moves on to the next phase:
+//
+//     OBJ -> OCT_ENTER -> LB_NODE -> LB_TRIS -> OCT_RETURN -> SHADE (batched)
+//
+// A step is small and loop-free (one octree node, one leaf-BVH node, <= 4 triangles, one
+// sibling step, one material evaluation), so divergence is bounded by the number of
+// distinct states instead of by trip counts.  The arithmetic of every step is the same
+// device function the per-lane walkers use (fs2_traverse.cuh, fs2_lbvh.cuh), so results
+// are bit-identical (tests/test_gpu_image.py compares all variants).
+//
+// Per-lane stacks live in shared memory, one 4-byte column per thread (conflict-free):
+//   octree frames   (FS2_PH_MESH_FRAMES + FS2_PH_SCENE_FRAMES) x 8 words
+//   leaf-BVH stack  FS2_PH_LB_STACK x 2 words
+#pragma once
+#include "fs2_shade.cuh"
+
+namespace fs2 {
+
+#define FS2_PH_THREADS 128
+#define FS2_PH_MESH_FRAMES 4   // mesh trees: internal nodes at depth 0..3 (mesh.cpp:16)
+#define FS2_PH_SCENE_FRAMES 5  // scene trees: internal nodes at depth 0..4 (<= ~2 M objects)
+#define FS2_PH_LB_STACK 18     // 6 inner leaf-BVH levels x 3 pending siblings
+#define FS2_PH_SLOTS ((FS2_PH_MESH_FRAMES + FS2_PH_SCENE_FRAMES) * 8 + FS2_PH_LB_STACK * 2)
+#define FS2_PH_SMEM_BYTES (FS2_PH_SLOTS * FS2_PH_THREADS * 4)
+
+#ifndef FS2_PH_SHADE_BATCH
+#define FS2_PH_SHADE_BATCH 8   // shade when this many lanes wait (or nothing else can run)
+#endif
+#ifndef FS2_PH_REPEAT_MIN
+#define FS2_PH_REPEAT_MIN 12   // repeat a phase only while this many lanes are still in it
+#endif
+
+enum PhState {
+  PH_IDLE = 0,
+  PH_SEG_START,   // begin Scene::Trace for the lane's ray
+  PH_OBJ,         // next object of the brute-force list / of the current scene-tree leaf
+  PH_ENTER,       // "call" octree node `cur`
+  PH_LB_NODE,     // visit leaf-BVH node `lb_cur`
+  PH_LB_TRIS,     // test one pending group of <= 4 triangles
+  PH_RETURN,      // return `ret` into the enclosing octree frame
+  PH_SHADE        // segment finished: material / sky / film, next ray
+};
+
+struct PhLane {
+  uint32_t st;
+  Hit rec;   // active record: scene-level best, or the leaf-local record of scene.cpp:84
+  Hit glob;  // scene-level best while a scene-tree leaf is processed
+  uint32_t obj_i;                              // brute-force cursor
+  uint32_t cur_obj;                            // mesh object being walked
+  uint32_t sleaf_first, sleaf_count, sleaf_i;  // scene-tree leaf iteration
+  uint32_t cur;                                // octree node to enter
+  int msp, ssp;                                // frame counts of the mesh / scene walk
+  uint32_t flags;                              // bit0 walking a mesh tree, bit1 ret, bit2 scene leaf improved
+  // leaf BVH walk
+  uint32_t lb_cur;
+  int lb_sp;
+  float bt, bu, bv;
+  uint32_t border;
+  uint32_t qbase, qcount, qmask;  // pending triangle groups of the current node; bit31 of qcount: found
+};
+
+#define PH_F_MESH 1u
+#define PH_F_RET 2u
+#define PH_F_SIMPROVED 4u
+#define PH_F_FOUND 8u
+
+// ---- shared-memory columns
+struct PhSmem {
+  uint32_t* col;  // &smem[threadIdx.x]
+  __device__ __forceinline__ uint32_t& w(int slot) const { return col[slot * FS2_PH_THREADS]; }
+  __device__ __forceinline__ float& f(int slot) const {
+    return reinterpret_cast<float*>(col)[slot * FS2_PH_THREADS];
+  }
+  // frame k (mesh frames first, then scene frames), word i
+  __device__ __forceinline__ int fslot(bool mesh, int sp, int i) const {
+    return ((mesh ? 0 : FS2_PH_MESH_FRAMES) + sp) * 8 + i;
+  }
+  __device__ __forceinline__ int lslot(int sp, int i) const {
+    return (FS2_PH_MESH_FRAMES + FS2_PH_SCENE_FRAMES) * 8 + sp * 2 + i;
+  }
+};
+
+// frame words: 0 node, 1 bits, 2..4 tx ty tz, 5..7 sx sy sz   (struct Frame, fs2_traverse.cuh)
+
+// ------------------------------------------------------------------ octree steps
+// "call" node w.cur of the active tree (reference mesh.cpp:78-84 / scene.cpp:76-83, then
+// bvh.h:160-186).  Same arithmetic as walk_octree().
+template <bool STATS>
+__device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& r,
+                                         const PhSmem& sm, Counters& c) {
+  const bool mesh = (w.flags & PH_F_MESH) != 0;
+  NodeRec n = load_node(S, w.cur);
+  float nparam;
+  V3 entry = r.start;
+  bool inside;
+  if (STATS) c.n_node++;
+  if (!ray_box(n.mn, n.mx, r, nparam, entry, inside) || nparam > w.rec.param) {
+    w.flags &= ~PH_F_RET;
+    w.st = PH_RETURN;
+    return;
+  }
+  if (n.count != FS_NODE_INTERNAL) {
+    if (!n.count) {
+      w.flags &= ~PH_F_RET;
+      w.st = PH_RETURN;
+    } else if (!mesh) {
+      // scene.cpp:84-99: one leaf-local record, seeded with "no hit"
+      w.sleaf_first = n.first;
+      w.sleaf_count = n.count;
+      w.sleaf_i = 0;
+      w.flags &= ~PH_F_SIMPROVED;
+      w.glob = w.rec;
+      w.rec = no_hit();
+      w.st = PH_OBJ;
+    } else {
+      // mesh leaf (mesh.cpp:86-111)
+      uint32_t root = __ldg(&S.lb_leaf[w.cur].x);
+      if (r.zero_length || (root == 0xFFFFFFFFu && n.count > 16u)) {
+        // rare: point query / leaf beyond the BVH level cap -> linear scan in reference order
+        bool ret = mesh_leaf<STATS>(S, n.first, n.count, r, w.cur_obj, w.rec, c);
+        w.flags = ret ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
+        w.st = PH_RETURN;
+      } else {
+        if (STATS) c.n_tri += n.count;
+        w.bt = w.rec.param;
+        w.bu = w.bv = 0.f;
+        w.border = 0;
+        w.flags &= ~PH_F_FOUND;
+        w.lb_sp = 0;
+        if (root == 0xFFFFFFFFu) {
+          w.qbase = n.first;
+          w.qcount = n.count;
+          w.qmask = (1u << ((n.count + 3u) >> 2)) - 1u;
+          w.st = PH_LB_TRIS;
+        } else {
+          w.lb_cur = root;
+          w.st = PH_LB_NODE;
+        }
+      }
+    }
+    return;
+  }
+  int& sp = mesh ? w.msp : w.ssp;
+  const int maxd = mesh ? FS2_PH_MESH_FRAMES : FS2_PH_SCENE_FRAMES;
+  if (sp >= maxd) {  // deeper than any tree the host builds
+    w.flags &= ~PH_F_RET;
+    w.st = PH_RETURN;
+    return;
+  }
+  V3 cen = (n.mn + n.mx) * 0.5f;
+  V3 st = inside ? r.start : entry;
+  uint32_t bits = (st.x - cen.x >= 0.0f ? 1u : 0u) | (st.z - cen.z >= 0.0f ? 2u : 0u) |
+                  (st.y - cen.y >= 0.0f ? 4u : 0u);
+  sm.w(sm.fslot(mesh, sp, 0)) = w.cur;
+  sm.w(sm.fslot(mesh, sp, 1)) = bits;
+  sm.f(sm.fslot(mesh, sp, 2)) = split_param(st.x, r.dir.x, cen.x);
+  sm.f(sm.fslot(mesh, sp, 3)) = split_param(st.y, r.dir.y, cen.y);
+  sm.f(sm.fslot(mesh, sp, 4)) = split_param(st.z, r.dir.z, cen.z);
+  sm.f(sm.fslot(mesh, sp, 5)) = st.x;
+  sm.f(sm.fslot(mesh, sp, 6)) = st.y;
+  sm.f(sm.fslot(mesh, sp, 7)) = st.z;
+  sp++;
+  w.cur = n.first + bits;
+  // stays in PH_ENTER
+}
+
+// Return (w.flags & PH_F_RET) into the enclosing frame of the active tree (bvh.h:189-228),
+// or finish the tree when no frame is left.  One frame per call.
+__device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray& r,
+                                          const PhSmem& sm) {
+  const bool mesh = (w.flags & PH_F_MESH) != 0;
+  int& sp = mesh ? w.msp : w.ssp;
+  bool ret = (w.flags & PH_F_RET) != 0;
+  if (sp == 0) {
+    if (!mesh) {  // Scene::Trace finished (scene.cpp:234-236)
+      w.st = PH_SHADE;
+      return;
+    }
+    // MeshObject::Trace finished with `ret` (mesh.cpp:277-322)
+    w.flags &= ~PH_F_MESH;
+    if (S.scene_root >= 0 && ret && w.rec.param < w.glob.param) {
+      w.glob = w.rec;
+      w.flags |= PH_F_SIMPROVED;
+    }
+    w.st = PH_OBJ;
+    return;
+  }
+  const int f = sp - 1;
+  uint32_t node = sm.w(sm.fslot(mesh, f, 0));
+  uint32_t bits = sm.w(sm.fslot(mesh, f, 1));
+  NodeRec pn = load_node(S, node);
+  if (ret) {
+    bits |= 32u;
+    NodeRec ch = load_node(S, pn.first + (bits & 7u));
+    if (point_in_box(ch.mn, ch.mx, r.start + r.dir * w.rec.param)) {
+      sp--;  // ret stays true; continue returning into the parent frame
+      return;
+    }
+  }
+  float tx = sm.f(sm.fslot(mesh, f, 2)), ty = sm.f(sm.fslot(mesh, f, 3)),
+        tz = sm.f(sm.fslot(mesh, f, 4));
+  uint32_t visits = ((bits >> 3) & 3u) + 1u;
+  bool x_hit = tx <= 1.0f, y_hit = ty <= 1.0f, z_hit = tz <= 1.0f;
+  float t = 0.f;
+  uint32_t flip = 0u;
+  int consumed = 0;
+  if (x_hit && tx < ty && tx < tz) {
+    t = tx;
+    consumed = 2;
+    flip = 1u;
+  } else if (y_hit && ty < tz && ty < tx) {
+    t = ty;
+    consumed = 3;
+    flip = 4u;
+  } else if (z_hit && tz < ty && tz < tx) {
+    t = tz;
+    consumed = 4;
+    flip = 2u;
+  }
+  bool go = flip != 0u && visits < 4u;
+  if (go) {
+    V3 st = v3(sm.f(sm.fslot(mesh, f, 5)), sm.f(sm.fslot(mesh, f, 6)), sm.f(sm.fslot(mesh, f, 7)));
+    go = point_in_box(pn.mn, pn.mx, st + r.dir * t);
+  }
+  if (!go) {
+    w.flags = (bits & 32u) ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
+    sp--;
+    return;  // keep returning
+  }
+  sm.f(sm.fslot(mesh, f, consumed)) = FS2_INFINITY;
+  bits = ((bits ^ flip) & ~(3u << 3)) | (visits << 3);
+  sm.w(sm.fslot(mesh, f, 1)) = bits;
+  w.cur = pn.first + (bits & 7u);
+  w.st = PH_ENTER;
+}
+
+// ------------------------------------------------------------------ object iteration
+// One object of the brute-force list (scene.cpp:230-233) or of the current scene-tree leaf
+// (scene.cpp:84-99).  Primitives are tested on the spot, a mesh starts its octree walk.
+template <bool STATS>
+__device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray& r, Counters& c) {
+  uint32_t oi;
+  const bool tree = S.scene_root >= 0;
+  if (!tree) {
+    if (w.obj_i >= S.n_objects) {
+      w.st = PH_SHADE;
+      return;
+    }
+    oi = w.obj_i++;
+  } else {
+    if (w.sleaf_i >= w.sleaf_count) {
+      // leaf done: hand the leaf's verdict back to the scene walk
+      w.rec = w.glob;
+      w.flags = (w.flags & PH_F_SIMPROVED) ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
+      w.st = PH_RETURN;
+      return;
+    }
+    oi = __ldg(S.scene_refs + w.sleaf_first + w.sleaf_i);
+    w.sleaf_i++;
+  }
+  float4 w0 = obj_word(S, oi, 0);
+  if (__float_as_uint(w0.x) == FS_OBJ_MESH) {
+    uint32_t root = __float_as_uint(w0.z);
+    if (root != 0xFFFFFFFFu) {
+      w.cur_obj = oi;
+      w.cur = root;
+      w.msp = 0;
+      w.flags |= PH_F_MESH;
+      w.st = PH_ENTER;
+    }
+    return;
+  }
+  bool improved = primitive_trace<STATS>(S, oi, __float_as_uint(w0.x), r, w.rec, c);
+  if (tree && improved && w.rec.param < w.glob.param) {
+    w.glob = w.rec;
+    w.flags |= PH_F_SIMPROVED;
+  }
+}
+
+// ------------------------------------------------------------------ leaf BVH steps
+// Leaf finished: publish the best of this leaf and return to the octree walk.
+__device__ __forceinline__ void ph_leaf_done(PhLane& w) {
+  if (w.flags & PH_F_FOUND) {
+    w.rec.param = w.bt;
+    w.rec.object = w.cur_obj;
+    w.rec.prim = w.border;
+    w.rec.u = w.bu;
+    w.rec.v = w.bv;
+    w.flags |= PH_F_RET;
+  } else {
+    w.flags &= ~PH_F_RET;
+  }
+  w.st = PH_RETURN;
+}
+
+// Next pending leaf-BVH node that can still matter, or leaf done.
+__device__ __forceinline__ void ph_lb_pop(PhLane& w, const PhSmem& sm) {
+  while (w.lb_sp > 0) {
+    --w.lb_sp;
+    float te = sm.f(sm.lslot(w.lb_sp, 1));
+    if (te <= fminf(w.bt, 1.0f)) {
+      w.lb_cur = sm.w(sm.lslot(w.lb_sp, 0));
+      w.st = PH_LB_NODE;
+      return;
+    }
+  }
+  ph_leaf_done(w);
+}
+
+template <bool STATS>
+__device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray& r,
+                                           const LbRay& q, const PhSmem& sm, Counters& c) {
+  const float4* nd = S.lb_nodes + 8 * (size_t)w.lb_cur;
+  float4 lx = __ldg(nd), ly = __ldg(nd + 1), lz = __ldg(nd + 2);
+  float4 hx = __ldg(nd + 3), hy = __ldg(nd + 4), hz = __ldg(nd + 5);
+  uint4 meta = __ldg((const uint4*)(nd + 6));
+  if (STATS) c.n_lbnode++;
+  const V3 s = r.start;
+  float lim = fminf(w.bt, 1.0f);
+  float t0 = lb_child(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, s, q, lim);
+  float t1 = lb_child(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, s, q, lim);
+  float t2 = lb_child(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, s, q, lim);
+  float t3 = lb_child(lx.w, ly.w, lz.w, hx.w, hy.w, hz.w, s, q, lim);
+  if (meta.y) {
+    uint32_t mask = (t0 < 3.0f ? 1u : 0u) | (t1 < 3.0f ? 2u : 0u) | (t2 < 3.0f ? 4u : 0u) |
+                    (t3 < 3.0f ? 8u : 0u);
+    if (mask) {
+      w.qbase = meta.x;
+      w.qcount = meta.z;
+      w.qmask = mask;
+      w.st = PH_LB_TRIS;
+    } else {
+      ph_lb_pop(w, sm);
+    }
+    return;
+  }
+  uint32_t c0 = meta.x, c1 = meta.x + 1, c2 = meta.x + 2, c3 = meta.x + 3;
+#define FS2_CSWAP(ta, ca, tb, cb) \
+  if (tb < ta) {                  \
+    float tt = ta;                \
+    ta = tb;                      \
+    tb = tt;                      \
+    uint32_t cc = ca;             \
+    ca = cb;                      \
+    cb = cc;                      \
+  }
+  FS2_CSWAP(t0, c0, t1, c1)
+  FS2_CSWAP(t2, c2, t3, c3)
+  FS2_CSWAP(t0, c0, t2, c2)
+  FS2_CSWAP(t1, c1, t3, c3)
+  FS2_CSWAP(t1, c1, t2, c2)
+#undef FS2_CSWAP
+  if (t3 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
+    sm.w(sm.lslot(w.lb_sp, 0)) = c3;
+    sm.f(sm.lslot(w.lb_sp, 1)) = t3;
+    w.lb_sp++;
+  }
+  if (t2 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
+    sm.w(sm.lslot(w.lb_sp, 0)) = c2;
+    sm.f(sm.lslot(w.lb_sp, 1)) = t2;
+    w.lb_sp++;
+  }
+  if (t1 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
+    sm.w(sm.lslot(w.lb_sp, 0)) = c1;
+    sm.f(sm.lslot(w.lb_sp, 1)) = t1;
+    w.lb_sp++;
+  }
+  if (t0 < 3.0f) {
+    w.lb_cur = c0;  // stays in PH_LB_NODE
+    return;
+  }
+  ph_lb_pop(w, sm);
+}
+
+template <bool STATS>
+__device__ __forceinline__ void ph_lb_tris(const DScene& S, PhLane& w, const Ray& r,
+                                           const PhSmem& sm, Counters& c) {
+  uint32_t g = (uint32_t)__ffs((int)w.qmask) - 1u;
+  w.qmask &= w.qmask - 1u;
+  uint32_t rem = w.qcount - 4u * g;
+  bool found = (w.flags & PH_F_FOUND) != 0;
+  lb_test_tris<STATS>(S, w.qbase + 4u * g, rem < 4u ? rem : 4u, r.start, r.dir, w.bt, w.border,
+                      found, w.bu, w.bv, c);
+  if (found) w.flags |= PH_F_FOUND;
+  if (!w.qmask) ph_lb_pop(w, sm);
+}
+
+}  // namespace fs2

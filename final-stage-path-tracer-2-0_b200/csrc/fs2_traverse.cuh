@@ -376,6 +376,10 @@ __device__ __forceinline__ bool sphere_test(V3 centre, float radius, const Ray& 
   return true;
 }
 
+template <bool STATS>
+__device__ __forceinline__ bool primitive_trace(const DScene& S, uint32_t oi, uint32_t type,
+                                                const Ray& r, Hit& h, Counters& c);
+
 // Per-segment context of the leaf-BVH variant (LB = true); unused otherwise.
 struct LbCtx {
   LbRay q;
@@ -397,6 +401,13 @@ __device__ __forceinline__ bool object_trace(const DScene& S, uint32_t oi, const
           return mesh_leaf<STATS>(S, first, count, r, oi, best, c);
         });
   }
+  return primitive_trace<STATS>(S, oi, type, r, h, c);
+}
+
+// The analytic primitives of reference source/object.cpp:23-237 (everything but meshes).
+template <bool STATS>
+__device__ __forceinline__ bool primitive_trace(const DScene& S, uint32_t oi, uint32_t type,
+                                                const Ray& r, Hit& h, Counters& c) {
   if (STATS) c.n_prim++;
   float4 w1 = obj_word(S, oi, 1), w2 = obj_word(S, oi, 2);
   // payload f[0..] = w1.z, w1.w, w2.x, w2.y, w2.z, w2.w, w3.x ...

@@ -196,7 +196,9 @@ typedef struct fs_camera {
 #define FS_TRACE_ASYNC 16     /* enqueue only: no stream synchronisation before returning */
 #define FS_TRACE_PER_THREAD 32 /* every thread scans its own mesh leaves linearly, in reference order */
 #define FS_TRACE_COOP 64       /* linear leaf scans done by the whole warp, 32 triangles per step */
-/* default (neither): every thread walks the per-leaf 4-wide BVH built by fs_scene_upload */
+#define FS_TRACE_LBVH_LANE 128 /* per-leaf 4-wide BVH walked by free-running lanes (nested loops) */
+/* default (none of the three): the per-leaf 4-wide BVH built by fs_scene_upload, walked by a
+ * warp-synchronous phase machine (all lanes in the same traversal state step together) */
 
 typedef struct fs_stats {
   uint64_t n_paths;    /* camera paths traced since the last reset           */
