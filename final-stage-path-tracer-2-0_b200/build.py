@@ -73,12 +73,31 @@ def build_host(force=False):
     return HOST_LIB
 
 
+CLI_DIR = os.path.join(PKG_DIR, "cli")
+CLI_EXE = os.path.join(PKG_DIR, "fs2_render")
+
+
+def build_cli(force=False):
+    """fs2_render: headless replacement of the reference's main.cpp (window/OpenGL loop)."""
+    src = os.path.join(CLI_DIR, "fs2_render.cpp")
+    deps = [src, os.path.join(HOST, "fs2_host.h")]
+    build_host()
+    if not force and not _newer(CLI_EXE, deps + [HOST_LIB]):
+        return CLI_EXE
+    cmd = ["g++", "-std=c++17", "-O2", "-Wall", "-I" + os.path.join(REPO_DIR, "include"), "-I" + HOST,
+           src, "-o", CLI_EXE, "-L" + PKG_DIR, "-lfs2host", "-lfs2cuda", "-Wl,-rpath,$ORIGIN",
+           "-lpthread"]
+    subprocess.run(cmd, check=True)
+    return CLI_EXE
+
+
 def build_all(force=False):
-    return build_cuda(force), build_host(force)
+    return build_cuda(force), build_host(force), build_cli(force)
 
 
 if __name__ == "__main__":
     import sys
     build_cuda(force=True, verbose="-v" in sys.argv)
     build_host(force=True)
+    build_cli(force=True)
     print(CUDA_LIB)

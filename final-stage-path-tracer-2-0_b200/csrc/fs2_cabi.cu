@@ -407,7 +407,7 @@ int fs_first_hit(fs_ctx* ctx, const fs_camera* cam, int width, int height, float
   uint32_t* d_mat = (uint32_t*)(base + n * 12);
   float* d_range = (float*)(base + n * 16);
   CamBasis cb = camera_basis(cam, width, height);
-  k_first_hit<<<pixel_grid(width, height), 128, 0, ctx->stream>>>(ctx->ds, cb, width, height, d_t,
+  k_first_hit<true><<<pixel_grid(width, height), 128, 0, ctx->stream>>>(ctx->ds, cb, width, height, d_t,
                                                                   d_obj, d_face, d_mat, d_range,
                                                                   ctx->d_stats);
   ctx->launches++;
@@ -444,7 +444,7 @@ int fs_trace_range(fs_ctx* ctx, const fs_camera* cam, int width, int height, flo
   one.half_w = -xd;
   one.half_h = -yd;
   float* d_range = (float*)ctx->scratch.p;
-  k_first_hit<<<dim3(1, 1), 128, 0, ctx->stream>>>(ctx->ds, one, 1, 1, nullptr, nullptr, nullptr,
+  k_first_hit<true><<<dim3(1, 1), 128, 0, ctx->stream>>>(ctx->ds, one, 1, 1, nullptr, nullptr, nullptr,
                                                   nullptr, d_range, ctx->d_stats);
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());

@@ -41,17 +41,21 @@ __device__ __forceinline__ bool pixel_of_thread(int width, int height, int& px, 
   return px < width && py < height;
 }
 
-__global__ void __launch_bounds__(128)
+// LB: mesh leaves are searched through the leaf BVH (default); false = the reference's linear
+// leaf loop (kept for A/B checks).
+template <bool LB>
+__global__ void __launch_bounds__(FS2_LB_THREADS)
 k_first_hit(DScene S, CamBasis cam, int width, int height, float* __restrict__ out_t,
             uint32_t* __restrict__ out_object, uint32_t* __restrict__ out_face,
             uint32_t* __restrict__ out_mat, float* __restrict__ out_range,
             unsigned long long* __restrict__ stats) {
+  __shared__ uint2 lb_stack[LB ? FS2_LB_STACK * FS2_LB_THREADS : 1];
   int px, py;
   bool valid = pixel_of_thread(width, height, px, py);
   Counters c = {0, 0, 0, 0, 0, 0};
   if (valid) {
     Ray r = camera_ray(cam, (float)px, (float)py, 0.0f, 0.0f);
-    Hit h = scene_trace<true>(S, r, c);
+    Hit h = scene_trace<true, LB>(S, r, c, lb_stack + (LB ? threadIdx.x : 0));
     size_t p = (size_t)py * width + px;
     bool got = h.object != 0xFFFFFFFFu;
     uint32_t face = 0xFFFFFFFFu, mat = S.sky_material;
@@ -74,6 +78,8 @@ k_first_hit(DScene S, CamBasis cam, int width, int height, float* __restrict__ o
   warp_add(stats + ST_TRI, c.n_tri);
   warp_add(stats + ST_BARY, c.n_bary);
   warp_add(stats + ST_PRIM, c.n_prim);
+  warp_add(stats + ST_LBNODE, c.n_lbnode);
+  warp_add(stats + ST_TRITEST, c.n_tritest);
 }
 
 // ------------------------------------------------------------------ path state
