@@ -332,7 +332,7 @@ def run_gpu(args, rank, world, local_rank):
         kms = sum(kernel_ms) / len(kernel_ms)
         roof = roofline(sst, objects, n_px, kms, peaks)
         try:
-            cpu = cpu_sample(scene_file) if world == 1 else None
+            cpu = cpu_sample(scene_file) if (world == 1 and not args.skip_cpu) else None
         except Exception as e:  # the reference binary did not travel
             cpu = {"value": None, "unit": "Mpaths/s", "cores": 0, "kind": "reference",
                    "sample": "unavailable: %s" % e}
@@ -366,6 +366,7 @@ def main():
     ap.add_argument("--steps", type=int, default=3)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="fs2")
+    ap.add_argument("--skip-cpu", action="store_true", help="tuning runs: no cpu_baseline leg")
     ap.add_argument("--variant", default="phase", choices=["phase", "lbvh_lane", "coop", "per_thread"],
                     help="leaf-scan variant of the trace kernel (A/B measurements)")
     args = ap.parse_args()

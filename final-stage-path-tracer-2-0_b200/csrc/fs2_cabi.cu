@@ -10,6 +10,7 @@
 #include <math.h>
 #include <stdarg.h>
 #include <stdio.h>
+#include <stdlib.h>
 #include <string.h>
 
 #include <string>
@@ -52,6 +53,7 @@ struct fs_ctx {
   uint64_t launches = 0;
   float last_trace_ms = 0.f, last_kernel_ms = 0.f;
   bool stats_build = false;
+  uint32_t tune = 2;  // FS2_TUNE
 };
 
 namespace {
@@ -250,6 +252,7 @@ int fs_create(fs_ctx** out, int device, int flags) {
   if (!ctx) return fail(nullptr, FS_E_NOMEM, "out of host memory");
   ctx->device = device;
   ctx->stats_build = (flags & 1) != 0;
+  if (const char* e = getenv("FS2_TUNE")) ctx->tune = (uint32_t)strtoul(e, nullptr, 0);
   int rc = set_device(ctx);
   if (rc == FS_OK) {
     cudaError_t e1 = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
@@ -481,7 +484,7 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
   CamBasis cb = camera_basis(cam, ctx->width, ctx->height);
   Film film{(float4*)ctx->sum.p, (float4*)ctx->aux.p, (uint32_t*)ctx->mat_id.p, ctx->width,
             ctx->height};
-  TraceParams tp{first_sample, n_samples, sample_stride, seed, flags};
+  TraceParams tp{first_sample, n_samples, sample_stride, seed, flags, ctx->tune};
   CUDA_TRY(ctx, cudaEventRecord(ctx->ev0, ctx->stream));
   CUDA_TRY(ctx, cudaEventRecord(ctx->evk0, ctx->stream));
   if (n_samples) {

@@ -89,6 +89,21 @@ struct PhSmem {
 
 // frame words: 0 node, 1 bits, 2..4 tx ty tz, 5..7 sx sy sz   (struct Frame, fs2_traverse.cuh)
 
+// Begin Scene::Trace for the lane's next ray (scene.cpp:227-237).
+__device__ __forceinline__ LbRay ph_segment_start(const DScene& S, PhLane& w, const Ray& r) {
+  w.rec = no_hit();
+  w.flags = 0;
+  w.ssp = 0;
+  if (S.scene_root < 0) {
+    w.obj_i = 0;
+    w.st = PH_OBJ;
+  } else {
+    w.cur = (uint32_t)S.scene_root;
+    w.st = PH_ENTER;
+  }
+  return make_lbray(r);
+}
+
 // ------------------------------------------------------------------ octree steps
 // "call" node w.cur of the active tree (reference mesh.cpp:78-84 / scene.cpp:76-83, then
 // bvh.h:160-186).  Same arithmetic as walk_octree().
