@@ -48,6 +48,8 @@ struct fs_ctx {
   // film
   int width = 0, height = 0;
   DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch;
+  DeviceBuf wf_planes, wf_list_a, wf_list_b, wf_counters;  // wavefront path state
+  int sm_count = 148;
   // stats
   unsigned long long* d_stats = nullptr;
   uint64_t launches = 0;
@@ -231,6 +233,57 @@ int collect_timing(fs_ctx* ctx) {
   return FS_OK;
 }
 
+// Wavefront pipeline (fs2_wavefront.cuh): k_wf_begin, then per wave k_wf_flip / k_wf_trace /
+// k_wf_shade until no slot is live.  A sample needs at most 8 segments (engine.cpp:16), so
+// 8 * n_samples waves always suffice; the synchronous form polls the live count every 16
+// waves and stops early, the asynchronous form enqueues the bound (empty waves exit at once).
+int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp,
+                     bool async) {
+  const uint32_t tiles_x = (uint32_t)(film.width + 15) / 16, tiles_y = (uint32_t)(film.height + 7) / 8;
+  const uint32_t cap = tiles_x * tiles_y * 128u;
+  int rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * FS2_WF_PLANES * 16))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_list_a, (size_t)cap * 4))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_list_b, (size_t)cap * 4))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_counters, 64))) return rc;
+  WfBuffers B;
+  B.planes = (float4*)ctx->wf_planes.p;
+  B.list_in = (uint32_t*)ctx->wf_list_b.p;
+  B.list_out = (uint32_t*)ctx->wf_list_a.p;
+  B.counters = (uint32_t*)ctx->wf_counters.p;
+  B.cap = cap;
+  B.tiles_x = tiles_x;
+  CUDA_TRY(ctx, cudaMemsetAsync(B.counters, 0, 64, ctx->stream));
+  k_wf_begin<<<cap / 128u, 128, 0, ctx->stream>>>(cb, film, tp, B);
+  ctx->launches++;
+  const uint32_t max_waves = 8u * tp.n_samples;
+  const int persistent = ctx->sm_count * 4;
+  uint32_t shade_blocks = cap / 128u;
+  for (uint32_t wave = 0; wave < max_waves; wave++) {
+    uint32_t* t = B.list_in;
+    B.list_in = B.list_out;
+    B.list_out = t;
+    k_wf_flip<<<1, 1, 0, ctx->stream>>>(B.counters);
+    if (ctx->stats_build)
+      k_wf_trace<true><<<persistent, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(ctx->ds, B, tp,
+                                                                                     ctx->d_stats);
+    else
+      k_wf_trace<false><<<persistent, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(ctx->ds, B, tp,
+                                                                                      ctx->d_stats);
+    k_wf_shade<<<shade_blocks, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
+    ctx->launches += 3;
+    if (!async && (wave & 15u) == 15u) {
+      uint32_t live = 0;
+      CUDA_TRY(ctx, cudaMemcpyAsync(&live, B.counters + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
+      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+      if (live == 0) break;
+      shade_blocks = (live + 127u) / 128u;  // the live count never grows
+    }
+  }
+  CUDA_TRY(ctx, cudaGetLastError());
+  return FS_OK;
+}
+
 }  // namespace
 
 extern "C" {
@@ -267,6 +320,14 @@ int fs_create(fs_ctx** out, int device, int flags) {
     if (e1 == cudaSuccess)
       e1 = cudaFuncSetAttribute(k_trace_phase<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 FS2_PH_SMEM_BYTES);
+    if (e1 == cudaSuccess)
+      e1 = cudaFuncSetAttribute(k_wf_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                FS2_PH_SMEM_BYTES);
+    if (e1 == cudaSuccess)
+      e1 = cudaFuncSetAttribute(k_wf_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                FS2_PH_SMEM_BYTES);
+    if (e1 == cudaSuccess)
+      e1 = cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);
     if (e1 == cudaSuccess) e1 = cudaMalloc(&ctx->d_stats, ST_COUNT * sizeof(unsigned long long));
     if (e1 == cudaSuccess)
       e1 = cudaMemset(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long));
@@ -288,7 +349,7 @@ int fs_destroy(fs_ctx* ctx) {
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
                       &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
-                      &ctx->scratch};
+                      &ctx->scratch, &ctx->wf_planes, &ctx->wf_list_a, &ctx->wf_list_b, &ctx->wf_counters};
   for (DeviceBuf* b : all) dev_free(b);
   if (ctx->d_stats) cudaFree(ctx->d_stats);
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
@@ -493,7 +554,10 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
     const bool coop = (flags & FS_TRACE_COOP) != 0;
     const bool st = ctx->stats_build;
 #define FS2_LAUNCH(K) K<<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats)
-    if (per_thread) {
+    if (flags & FS_TRACE_WAVEFRONT) {
+      if ((rc = launch_wavefront(ctx, cb, film, tp, (flags & FS_TRACE_ASYNC) != 0))) return rc;
+      ctx->launches--;  // the common increment below counts one launch
+    } else if (per_thread) {
       if (st) FS2_LAUNCH((k_trace_mega<true, false>)); else FS2_LAUNCH((k_trace_mega<false, false>));
     } else if (coop) {
       if (st) FS2_LAUNCH(k_trace_coop<true>); else FS2_LAUNCH(k_trace_coop<false>);

@@ -22,7 +22,7 @@ struct TraceParams {
   uint32_t first_sample, n_samples, sample_stride;
   uint64_t seed;
   int flags;
-  uint32_t tune;  // scheduling knobs of k_trace_phase (env FS2_TUNE): bits 0-3 age shift, 15 = no aging
+  uint32_t tune;  // experiment knob (env FS2_TUNE), see the kernels that read it
 };
 
 // stats slots (device array of unsigned long long)
@@ -346,45 +346,37 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
   LbRay q = make_lbray(ps.ray);
   if (mine) {
     begin_path(cam, tp, pixel, px, py, ps);
-    q = ph_segment_start(S, w, ps.ray);
+    w.st = PH_SEG_START;
   }
-  // Majority scheduling: every iteration the warp runs the one phase that most lanes wait
-  // for (lanes that were passed over gain priority with age, so nobody falls behind and
-  // ends up walking alone at the end of the launch).
-  uint32_t age = 0;
   for (;;) {
-    unsigned peers = __match_any_sync(0xFFFFFFFFu, w.st);
-    uint32_t votes = (uint32_t)__popc(peers) + min(age >> (tp.tune & 15u), 32u);
-    uint32_t key = (w.st == PH_IDLE) ? 0u : ((votes << 4) | w.st);
-    uint32_t top = __reduce_max_sync(0xFFFFFFFFu, key);
-    if (top == 0u) break;  // every lane is idle
-    const uint32_t sel = top & 15u;
-    const bool run = w.st == sel;
-    age = run ? 0u : age + 1u;
-    switch (sel) {  // warp-uniform
-      case PH_OBJ:
-        if (run) ph_object<STATS>(S, w, ps.ray, c);
-        break;
-      case PH_ENTER:
-        if (run) ph_enter<STATS>(S, w, ps.ray, sm, c);
-        break;
-      case PH_LB_NODE:
-        if (run) ph_lb_node<STATS>(S, w, ps.ray, q, sm, c);
-        break;
-      case PH_LB_TRIS:
-        if (run) ph_lb_tris<STATS>(S, w, ps.ray, sm, c);
-        break;
-      case PH_RETURN:
-        if (run) ph_return(S, w, ps.ray, sm);
-        break;
-      default:  // PH_SHADE
-        if (run) {
-          n_seg++;
-          bool alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, w.rec, n_shade);
-          if (alive) q = ph_segment_start(S, w, ps.ray);
-          else w.st = PH_IDLE;
-        }
-        break;
+    if (w.st == PH_SEG_START) {  // scene.cpp:227-237
+      w.rec = no_hit();
+      w.flags = 0;
+      w.ssp = 0;
+      q = make_lbray(ps.ray);
+      if (S.scene_root < 0) {
+        w.obj_i = 0;
+        w.st = PH_OBJ;
+      } else {
+        w.cur = (uint32_t)S.scene_root;
+        w.st = PH_ENTER;
+      }
+    }
+    FS2_PHASE(PH_OBJ, 3, ph_object<STATS>(S, w, ps.ray, c))
+    FS2_PHASE(PH_ENTER, 2, ph_enter<STATS>(S, w, ps.ray, sm, c))
+    FS2_PHASE(PH_LB_NODE, 2, ph_lb_node<STATS>(S, w, ps.ray, q, sm, c))
+    FS2_PHASE(PH_LB_TRIS, 2, ph_lb_tris<STATS>(S, w, ps.ray, sm, c))
+    FS2_PHASE(PH_RETURN, 4, ph_return(S, w, ps.ray, sm))
+    unsigned m_shade = __ballot_sync(0xFFFFFFFFu, w.st == PH_SHADE);
+    unsigned m_busy = __ballot_sync(0xFFFFFFFFu, w.st != PH_SHADE && w.st != PH_IDLE);
+    if (m_shade && (__popc(m_shade) >= FS2_PH_SHADE_BATCH || !m_busy)) {
+      if (w.st == PH_SHADE) {
+        n_seg++;
+        bool alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, w.rec, n_shade);
+        w.st = alive ? PH_SEG_START : PH_IDLE;
+      }
+    } else if (!m_busy) {
+      break;  // every lane is idle
     }
   }
   if (mine) film_add(film, pixel, ps.sum, tp.n_samples);
@@ -400,6 +392,10 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
     warp_add(stats + ST_TRITEST, c.n_tritest);
   }
 }
+
+}  // namespace fs2
+#include "fs2_wavefront.cuh"
+namespace fs2 {
 
 // reference source/frame.cpp:56-69: mean and display RGB8 = 255*pow(sat(mean), 1/2.2) + 0.5
 __global__ void __launch_bounds__(256)

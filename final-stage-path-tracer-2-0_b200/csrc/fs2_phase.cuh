@@ -139,7 +139,7 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
       uint32_t root = __ldg(&S.lb_leaf[w.cur].x);
       if (r.zero_length || (root == 0xFFFFFFFFu && n.count > 16u)) {
         // rare: point query / leaf beyond the BVH level cap -> linear scan in reference order
-        bool ret = mesh_leaf<STATS>(S, n.first, n.count, r, w.cur_obj, w.rec, c);
+        bool ret = mesh_leaf_cold<STATS>(S, n.first, n.count, r, w.cur_obj, w.rec, c);
         w.flags = ret ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
         w.st = PH_RETURN;
       } else {

@@ -110,26 +110,25 @@ __device__ __forceinline__ bool ray_box(V3 mn, V3 mx, const Ray& r, float& param
     param = 0.0f;
     return inside;
   }
-  if (inside) {
-    if (point_in_box(mn, mx, r.stop)) {
-      param = 0.0f;
-      return true;
-    }
-    float p;
-    if (box_worker(mn, mx, r.stop, r.start - r.stop, p)) {
-      param = 1.0f - p;
-      return true;
-    }
-    return false;
-  }
-  // the worker recomputes stop - start; for bounce rays this is not bit-equal to r.dir
-  // (engine.cpp:120-127 offsets start and dir separately)
-  V3 vec = r.stop - r.start;
-  if (box_worker(mn, mx, r.start, vec, param)) {
-    entry = r.start + vec * param;
+  if (inside && point_in_box(mn, mx, r.stop)) {
+    param = 0.0f;
     return true;
   }
-  return false;
+  // One instance of the slab worker serves both cases (code size: the traversal loop has
+  // to stay inside the 32 KB instruction cache).  Inside origin: the reversed segment
+  // (intersect.cpp:621-649); outside: the worker recomputes stop - start, which for bounce
+  // rays is not bit-equal to r.dir (engine.cpp:120-127 offsets start and dir separately).
+  V3 o = inside ? r.stop : r.start;
+  V3 vec = inside ? (r.start - r.stop) : (r.stop - r.start);
+  float p;
+  if (!box_worker(mn, mx, o, vec, p)) return false;
+  if (inside) {
+    param = 1.0f - p;
+  } else {
+    param = p;
+    entry = r.start + vec * p;
+  }
+  return true;
 }
 
 // ------------------------------------------------------------------ triangles
@@ -210,6 +209,14 @@ __device__ __forceinline__ bool mesh_leaf(const DScene& S, uint32_t first, uint3
 }  // namespace fs2
 #include "fs2_lbvh.cuh"
 namespace fs2 {
+
+// Out-of-line copy for the rare callers inside the phase machine (zero-length rays, leaves
+// beyond the leaf-BVH level cap).
+template <bool STATS>
+__device__ __noinline__ bool mesh_leaf_cold(const DScene& S, uint32_t first, uint32_t count,
+                                            const Ray& r, uint32_t object, Hit& h, Counters& c) {
+  return mesh_leaf<STATS>(S, first, count, r, object, h, c);
+}
 
 // ------------------------------------------------------------------ octree walker
 // Frame of one internal node whose children are being visited (bvh.h:154-231).

@@ -99,24 +99,25 @@ def test_aux_buffers_match_oracle_without_jitter(ctx):
 
 def _variants_agree(ctx, scene, cam, w, h, spp):
     """default (leaf BVH, warp-synchronous phase machine), leaf BVH walked by free-running
-    lanes, warp-cooperative linear scan and per-thread linear scan (the reference's loop
+    lanes, the wavefront pipeline (separate trace / shade kernels, state in HBM), warp-cooperative linear scan and per-thread linear scan (the reference's loop
     order) must produce identical hits: same seeds -> identical films, aux
     buffers, ids and reference-equivalent work counters."""
     import fs2_b200
     ctx.upload(scene)
     ctx.resize(w, h)
     out = []
-    for flags in (0, fs2_b200.FS_TRACE_LBVH_LANE, fs2_b200.FS_TRACE_COOP,
-                  fs2_b200.FS_TRACE_PER_THREAD):
+    for flags in (0, fs2_b200.FS_TRACE_LBVH_LANE, fs2_b200.FS_TRACE_WAVEFRONT,
+                  fs2_b200.FS_TRACE_COOP, fs2_b200.FS_TRACE_PER_THREAD):
         ctx.reset()
         ctx.reset_stats()
         ctx.trace(cam, spp, seed=11, flags=flags)
         f = ctx.read_film(aux=True)
         out.append((f, ctx.stats()))
-    (fl, sl), (fl2, sl2), (fa, sa), (fb, sb) = out
+    (fl, sl), (fl2, sl2), (fw, sw), (fa, sa), (fb, sb) = out
     for k in ("n_paths", "n_segments", "n_node", "n_tri", "n_prim", "n_shade"):
         assert sl[k] == sl2[k], k  # same rays, same reference-equivalent work
-    for f in (fl, fl2, fa):
+        assert sl[k] == sw[k], k
+    for f in (fl, fl2, fw, fa):
         assert (f["mean"].view(np.uint32) == fb["mean"].view(np.uint32)).all()
         assert (f["normal"].view(np.uint32) == fb["normal"].view(np.uint32)).all()
         assert (f["depth"].view(np.uint32) == fb["depth"].view(np.uint32)).all()
