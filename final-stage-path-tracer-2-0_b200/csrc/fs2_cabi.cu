@@ -48,7 +48,9 @@ struct fs_ctx {
   // film
   int width = 0, height = 0;
   DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch;
-  DeviceBuf wf_planes, wf_list_a, wf_list_b, wf_counters;  // wavefront path state
+  DeviceBuf wf_planes, wf_hit, wf_counters;  // wavefront path state
+  uint32_t* wf_host_live = nullptr;   // pinned: live paths of the newest wave
+  cudaEvent_t wf_events[4] = {};
   int sm_count = 148;
   // stats
   unsigned long long* d_stats = nullptr;
@@ -233,52 +235,62 @@ int collect_timing(fs_ctx* ctx) {
   return FS_OK;
 }
 
-// Wavefront pipeline (fs2_wavefront.cuh): k_wf_begin, then per wave k_wf_flip / k_wf_trace /
-// k_wf_shade until no slot is live.  A sample needs at most 8 segments (engine.cpp:16), so
-// 8 * n_samples waves always suffice; the synchronous form polls the live count every 16
-// waves and stops early, the asynchronous form enqueues the bound (empty waves exit at once).
-int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp,
-                     bool async) {
+// Wavefront pipeline (fs2_wavefront.cuh): fill the pool, then per wave k_wf_flip / k_wf_trace /
+// k_wf_shade until no path is live.  The host never drains the stream: k_wf_flip publishes the
+// live count of the wave it starts in a pinned host word, the host keeps FS2_WF_AHEAD waves
+// enqueued (event ring) and stops enqueueing once a wave reported zero live paths; the waves
+// already in the queue then exit at once.
+#define FS2_WF_AHEAD 4
+int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
   const uint32_t tiles_x = (uint32_t)(film.width + 15) / 16, tiles_y = (uint32_t)(film.height + 7) / 8;
-  const uint32_t cap = tiles_x * tiles_y * 128u;
+  const uint32_t pix_cap = tiles_x * tiles_y * 128u;
+  const unsigned long long total = (unsigned long long)pix_cap * tp.n_samples;
+  uint32_t cap = FS2_WF_MAX_PATHS;
+  if (ctx->tune >> 8) cap = (ctx->tune >> 8) << 10;  // FS2_TUNE bits 8..: pool size in 1024 paths
+  if ((unsigned long long)cap > total) cap = (uint32_t)((total + 127u) & ~127ull);
   int rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * FS2_WF_PLANES * 16))) return rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_list_a, (size_t)cap * 4))) return rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_list_b, (size_t)cap * 4))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * FS2_WF_PLANES * 16 * 2))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_hit, (size_t)cap * 20))) return rc;
   if ((rc = dev_alloc(ctx, &ctx->wf_counters, 64))) return rc;
+  if (!ctx->wf_host_live) {
+    CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->wf_host_live, 64, cudaHostAllocMapped));
+    for (int i = 0; i < FS2_WF_AHEAD; i++)
+      CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_events[i], cudaEventDisableTiming));
+  }
   WfBuffers B;
-  B.planes = (float4*)ctx->wf_planes.p;
-  B.list_in = (uint32_t*)ctx->wf_list_b.p;
-  B.list_out = (uint32_t*)ctx->wf_list_a.p;
+  B.state[0] = (float4*)ctx->wf_planes.p;
+  B.state[1] = B.state[0] + (size_t)cap * FS2_WF_PLANES;
+  B.hit = (float4*)ctx->wf_hit.p;
+  B.hit_v = (float*)(B.hit + cap);
   B.counters = (uint32_t*)ctx->wf_counters.p;
+  B.host_live = ctx->wf_host_live;
   B.cap = cap;
+  B.pix_cap = pix_cap;
   B.tiles_x = tiles_x;
+  B.total = total;
+  *(volatile uint32_t*)ctx->wf_host_live = 1u;
   CUDA_TRY(ctx, cudaMemsetAsync(B.counters, 0, 64, ctx->stream));
-  k_wf_begin<<<cap / 128u, 128, 0, ctx->stream>>>(cb, film, tp, B);
+  k_wf_shade<true><<<cap / 128u, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
   ctx->launches++;
-  const uint32_t max_waves = 8u * tp.n_samples;
+  // every path has at most 8 segments and the pool is refilled every wave
+  const unsigned long long max_waves = 8ull * ((total + cap - 1) / cap) + 8ull;
   const int persistent = ctx->sm_count * 4;
-  uint32_t shade_blocks = cap / 128u;
-  for (uint32_t wave = 0; wave < max_waves; wave++) {
-    uint32_t* t = B.list_in;
-    B.list_in = B.list_out;
-    B.list_out = t;
-    k_wf_flip<<<1, 1, 0, ctx->stream>>>(B.counters);
+  const uint32_t shade_blocks = cap / 128u;
+  for (unsigned long long wave = 0; wave < max_waves; wave++) {
+    if (wave >= FS2_WF_AHEAD) {
+      CUDA_TRY(ctx, cudaEventSynchronize(ctx->wf_events[wave % FS2_WF_AHEAD]));
+      if (*(volatile uint32_t*)ctx->wf_host_live == 0u) break;
+    }
+    k_wf_flip<<<1, 1, 0, ctx->stream>>>(B.counters, B.host_live);
+    CUDA_TRY(ctx, cudaEventRecord(ctx->wf_events[wave % FS2_WF_AHEAD], ctx->stream));
     if (ctx->stats_build)
       k_wf_trace<true><<<persistent, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(ctx->ds, B, tp,
                                                                                      ctx->d_stats);
     else
       k_wf_trace<false><<<persistent, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(ctx->ds, B, tp,
                                                                                       ctx->d_stats);
-    k_wf_shade<<<shade_blocks, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
+    k_wf_shade<false><<<shade_blocks, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
     ctx->launches += 3;
-    if (!async && (wave & 15u) == 15u) {
-      uint32_t live = 0;
-      CUDA_TRY(ctx, cudaMemcpyAsync(&live, B.counters + 1, 4, cudaMemcpyDeviceToHost, ctx->stream));
-      CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-      if (live == 0) break;
-      shade_blocks = (live + 127u) / 128u;  // the live count never grows
-    }
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return FS_OK;
@@ -349,9 +361,13 @@ int fs_destroy(fs_ctx* ctx) {
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
                       &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
-                      &ctx->scratch, &ctx->wf_planes, &ctx->wf_list_a, &ctx->wf_list_b, &ctx->wf_counters};
+                      &ctx->scratch, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters};
   for (DeviceBuf* b : all) dev_free(b);
   if (ctx->d_stats) cudaFree(ctx->d_stats);
+  if (ctx->wf_host_live) {
+    cudaFreeHost(ctx->wf_host_live);
+    for (cudaEvent_t e : ctx->wf_events) cudaEventDestroy(e);
+  }
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
   if (ctx->evk0) cudaEventDestroy(ctx->evk0);
@@ -555,7 +571,7 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
     const bool st = ctx->stats_build;
 #define FS2_LAUNCH(K) K<<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats)
     if (flags & FS_TRACE_WAVEFRONT) {
-      if ((rc = launch_wavefront(ctx, cb, film, tp, (flags & FS_TRACE_ASYNC) != 0))) return rc;
+      if ((rc = launch_wavefront(ctx, cb, film, tp))) return rc;
       ctx->launches--;  // the common increment below counts one launch
     } else if (per_thread) {
       if (st) FS2_LAUNCH((k_trace_mega<true, false>)); else FS2_LAUNCH((k_trace_mega<false, false>));

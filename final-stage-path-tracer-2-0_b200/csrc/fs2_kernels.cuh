@@ -115,16 +115,13 @@ __device__ __forceinline__ void begin_path(const CamBasis& cam, const TraceParam
 }
 
 // Everything TraceStep does around Scene::Trace (reference source/engine.cpp:59-159) for the
-// segment whose nearest hit is `h`, in forward form; then either the next segment's ray is
-// in ps.ray, or the path is finished and the pixel's next sample (if any) is started.
-// Returns false when the lane has rendered all its samples.  The aux buffers of the film
-// are written by the last sample of the launch (frame.cpp:78-85: last sample wins).
-__device__ __forceinline__ bool finish_segment(const DScene& S, const CamBasis& cam,
-                                               const Film& film, const TraceParams& tp,
-                                               uint32_t pixel, int px, int py, PathState& ps,
-                                               const Hit& h, uint32_t& n_shade) {
+// segment whose nearest hit is `h`, in forward form.  Returns true when the path is finished
+// (its radiance is ps.L); otherwise the next segment's ray is in ps.ray.  The aux buffers of
+// the film are written by the last sample of the launch (frame.cpp:78-85: last sample wins).
+__device__ __forceinline__ bool shade_segment(const DScene& S, const CamBasis& cam,
+                                              const Film& film, uint32_t pixel, bool last,
+                                              PathState& ps, const Hit& h, uint32_t& n_shade) {
   const bool got = h.object != 0xFFFFFFFFu;
-  const bool last = ps.s + 1 == tp.n_samples;
   bool done = false;
 
   if (ps.fog_pending) {
@@ -197,7 +194,16 @@ __device__ __forceinline__ bool finish_segment(const DScene& S, const CamBasis& 
     }
   }
 
-  if (done) {
+  return done;
+}
+
+// shade_segment, then — when the path is finished — the pixel's next sample (if any) is
+// started.  Returns false when the lane has rendered all its samples.
+__device__ __forceinline__ bool finish_segment(const DScene& S, const CamBasis& cam,
+                                               const Film& film, const TraceParams& tp,
+                                               uint32_t pixel, int px, int py, PathState& ps,
+                                               const Hit& h, uint32_t& n_shade) {
+  if (shade_segment(S, cam, film, pixel, ps.s + 1 == tp.n_samples, ps, h, n_shade)) {
     ps.sum = ps.sum + ps.L;
     ps.s++;
     if (ps.s == tp.n_samples) return false;

@@ -6,42 +6,58 @@
 // caches are ~6 KB L0 / 32 KB L1.5 per SM, so warps that sit in different phases keep
 // refetching code from L2: 34-56 % of all warp stall samples are "no instruction", issue
 // slots are 27-34 % busy, and DRAM moves 0.01 % of peak.  Splitting at the segment boundary
-// makes the traversal loop a small kernel and pays ~300 B of state traffic per segment —
+// makes the traversal loop a small kernel and pays ~250 B of state traffic per segment —
 // bandwidth this path otherwise leaves idle.
 //
-//   k_wf_begin   one thread per pixel slot: first camera ray, compacted list of live slots
-//   k_wf_flip    device-side counter hand-over between waves (no host round trip)
-//   k_wf_trace   persistent warps; lanes pull rays from the live list in chunks and walk
-//                them with the phase machine of fs2_phase.cuh; writes the nearest hit
-//   k_wf_shade   one thread per live slot: TraceStep's bookkeeping for the finished segment
-//                (finish_segment, fs2_kernels.cuh), next ray or next sample, film add when the
-//                pixel's samples are done; live slots are re-compacted with ballot + one
-//                atomic per warp
+// A *pool* of `cap` paths is in flight (not one per pixel: profiles/r1_f showed that with one
+// ray per pixel the wave count is the longest pixel's segment count, 8 x spp, and the sparse
+// tail waves cost as much as full ones).  Path ids = (sample, pixel slot) are handed out from
+// one 64-bit counter, sample-major and in pixel-tile order, so a warp that regenerates lanes
+// gets neighbouring pixels of the same sample.
 //
-// Slot = pixel (tile order of pixel_of_thread), so a slot always has exactly one ray in
-// flight until its samples are exhausted; arithmetic is the megakernel's, bit for bit.
+//   k_wf_shade<true>   fills the pool with the first `cap` camera paths
+//   k_wf_flip          device-side counter hand-over between waves (no host round trip)
+//   k_wf_trace         persistent warps; lanes pull rays from the current state array in
+//                      chunks and walk them with the phase machine of fs2_phase.cuh; writes
+//                      the nearest hit
+//   k_wf_shade<false>  one thread per live path: TraceStep's bookkeeping for the finished
+//                      segment (shade_segment, fs2_kernels.cuh).  A finished path adds its
+//                      radiance to the film (one 16-byte vector atomic) and the lane takes
+//                      the next path id; live lanes write their state *compacted* into the
+//                      other state array (ballot + one atomic per warp), so every wave reads
+//                      and writes dense, coalesced planes and there are no index lists.
+//
+// The per-path arithmetic is the megakernel's, bit for bit, and so is every path's RNG stream
+// (keyed by seed, pixel, sample); only the order in which a pixel's samples are added to the
+// film differs (float atomics), so films agree to rounding, not bit for bit.
 #pragma once
 #include "fs2_phase.cuh"
 
 namespace fs2 {
 
-#define FS2_WF_PLANES 9      // float4 planes of per-slot state
-#define FS2_WF_CHUNK 128     // ray indices a warp reserves per atomic
+#define FS2_WF_PLANES 6          // float4 planes of per-path state
+#define FS2_WF_CHUNK 128         // most ray indices a warp reserves per atomic
+#define FS2_WF_MAX_PATHS (1u << 22)  // pool size bound (state: 2 x 96 B + 20 B per path)
 
+// counters (uint32): 0 n_in, 1 n_out, 2 fetch cursor of k_wf_trace, 3 current state array,
+//                    4-5 next path id (uint64), 6 waves run
 struct WfBuffers {
-  float4* planes;      // [FS2_WF_PLANES][cap]
-  uint32_t* list_in;   // live slots of this wave
-  uint32_t* list_out;  // live slots of the next wave
-  uint32_t* counters;  // 0: n_in, 1: n_out, 2: fetch cursor
-  uint32_t cap;        // slots = padded pixel tiles
+  float4* state[2];   // [FS2_WF_PLANES][cap], ping-pong
+  float4* hit;        // [cap] param, object, prim, u   (same index as the ray of this wave)
+  float* hit_v;       // [cap]
+  uint32_t* counters;
+  uint32_t* host_live;  // pinned host word: live paths at the start of the newest wave
+  uint32_t cap;         // paths in flight
+  uint32_t pix_cap;     // pixel slots = padded 16x8 tiles x 128
   uint32_t tiles_x;
+  unsigned long long total;  // path ids: pix_cap x n_samples (ids of padding pixels are skipped)
 };
 
 // plane layout
-//  0: ray.start.xyz, ray.dir.x      1: ray.stop.xyz, ray.dir.y     2: ray.dir.z, zero_length, meta, s
-//  3: L.xyz, T.x                    4: T.y, T.z, sum.x, sum.y      5: sum.z, rng lo, rng hi, fog_mat
-//  6: fog_pos.xyz, -                7: hit param, object, prim, u  8: hit v, -, -, -
-// meta = depth | fog_pending << 8
+//  0: ray.start.xyz, ray.dir.x      1: ray.stop.xyz, ray.dir.y
+//  2: ray.dir.z, meta, pixel slot, sample      meta = zero_length | depth << 8 | fog_pending << 16
+//  3: L.xyz, T.x                    4: T.y, T.z, rng lo, rng hi
+//  5: fog_pos.xyz, fog_mat          (written / read only while a fog decision is pending)
 
 __device__ __forceinline__ void wf_slot_pixel(const WfBuffers& B, uint32_t slot, int& px, int& py) {
   uint32_t block = slot >> 7, t = slot & 127u;
@@ -50,112 +66,89 @@ __device__ __forceinline__ void wf_slot_pixel(const WfBuffers& B, uint32_t slot,
   py = (int)((block / B.tiles_x) * 8u + (warp >> 1) * 4u + (lane >> 3));
 }
 
-__device__ __forceinline__ void wf_store_ray(const WfBuffers& B, uint32_t slot, const PathState& ps) {
-  float4* p = B.planes + slot;
-  p[0 * (size_t)B.cap] = make_float4(ps.ray.start.x, ps.ray.start.y, ps.ray.start.z, ps.ray.dir.x);
-  p[1 * (size_t)B.cap] = make_float4(ps.ray.stop.x, ps.ray.stop.y, ps.ray.stop.z, ps.ray.dir.y);
-  uint32_t meta = ps.depth | (ps.fog_pending ? 256u : 0u);
-  p[2 * (size_t)B.cap] = make_float4(ps.ray.dir.z, __uint_as_float(ps.ray.zero_length ? 1u : 0u),
-                                     __uint_as_float(meta), __uint_as_float(ps.s));
+__device__ __forceinline__ void wf_store_path(float4* st, uint32_t cap, uint32_t i,
+                                              const PathState& ps, uint32_t pixslot) {
+  float4* p = st + i;
+  const size_t c = cap;
+  uint32_t meta = (ps.ray.zero_length ? 1u : 0u) | (ps.depth << 8) | (ps.fog_pending ? 65536u : 0u);
+  __stcs(p, make_float4(ps.ray.start.x, ps.ray.start.y, ps.ray.start.z, ps.ray.dir.x));
+  __stcs(p + c, make_float4(ps.ray.stop.x, ps.ray.stop.y, ps.ray.stop.z, ps.ray.dir.y));
+  __stcs(p + 2 * c, make_float4(ps.ray.dir.z, __uint_as_float(meta), __uint_as_float(pixslot),
+                                __uint_as_float(ps.s)));
+  __stcs(p + 3 * c, make_float4(ps.L.x, ps.L.y, ps.L.z, ps.T.x));
+  __stcs(p + 4 * c, make_float4(ps.T.y, ps.T.z, __uint_as_float((uint32_t)ps.rng.s),
+                                __uint_as_float((uint32_t)(ps.rng.s >> 32))));
+  if (ps.fog_pending)
+    __stcs(p + 5 * c, make_float4(ps.fog_pos.x, ps.fog_pos.y, ps.fog_pos.z, __uint_as_float(ps.fog_mat)));
 }
 
-__device__ __forceinline__ void wf_store_path(const WfBuffers& B, uint32_t slot, const PathState& ps) {
-  wf_store_ray(B, slot, ps);
-  float4* p = B.planes + slot;
-  p[3 * (size_t)B.cap] = make_float4(ps.L.x, ps.L.y, ps.L.z, ps.T.x);
-  p[4 * (size_t)B.cap] = make_float4(ps.T.y, ps.T.z, ps.sum.x, ps.sum.y);
-  p[5 * (size_t)B.cap] = make_float4(ps.sum.z, __uint_as_float((uint32_t)ps.rng.s),
-                                     __uint_as_float((uint32_t)(ps.rng.s >> 32)),
-                                     __uint_as_float(ps.fog_mat));
-  if (ps.fog_pending) p[6 * (size_t)B.cap] = make_float4(ps.fog_pos.x, ps.fog_pos.y, ps.fog_pos.z, 0.f);
-}
-
-__device__ __forceinline__ Ray wf_load_ray(const WfBuffers& B, uint32_t slot) {
-  const float4* p = B.planes + slot;
-  float4 a = p[0], b = p[1 * (size_t)B.cap], c = p[2 * (size_t)B.cap];
+__device__ __forceinline__ Ray wf_load_ray(const float4* st, uint32_t cap, uint32_t i) {
+  const float4* p = st + i;
+  const size_t c = cap;
+  float4 a = __ldcs(p), b = __ldcs(p + c), d = __ldcs(p + 2 * c);
   Ray r;
   r.start = v3(a.x, a.y, a.z);
   r.stop = v3(b.x, b.y, b.z);
-  r.dir = v3(a.w, b.w, c.x);
-  r.zero_length = __float_as_uint(c.y) != 0u;
+  r.dir = v3(a.w, b.w, d.x);
+  r.zero_length = (__float_as_uint(d.y) & 1u) != 0u;
   return r;
 }
 
-__device__ __forceinline__ void wf_load_path(const WfBuffers& B, uint32_t slot, PathState& ps, Hit& h) {
-  const float4* p = B.planes + slot;
-  float4 a = p[0], b = p[1 * (size_t)B.cap], c = p[2 * (size_t)B.cap];
-  float4 d = p[3 * (size_t)B.cap], e = p[4 * (size_t)B.cap], f = p[5 * (size_t)B.cap];
-  float4 hh = p[7 * (size_t)B.cap], hi = p[8 * (size_t)B.cap];
+__device__ __forceinline__ void wf_load_path(const WfBuffers& B, const float4* st, uint32_t i,
+                                             PathState& ps, uint32_t& pixslot, Hit& h) {
+  const float4* p = st + i;
+  const size_t c = B.cap;
+  float4 a = __ldcs(p), b = __ldcs(p + c), d = __ldcs(p + 2 * c);
+  float4 e = __ldcs(p + 3 * c), f = __ldcs(p + 4 * c);
+  float4 hh = __ldcs(B.hit + i);
+  float hv = __ldcs(B.hit_v + i);
   ps.ray.start = v3(a.x, a.y, a.z);
   ps.ray.stop = v3(b.x, b.y, b.z);
-  ps.ray.dir = v3(a.w, b.w, c.x);
-  ps.ray.zero_length = __float_as_uint(c.y) != 0u;
-  uint32_t meta = __float_as_uint(c.z);
-  ps.depth = meta & 255u;
-  ps.fog_pending = (meta & 256u) != 0u;
-  ps.s = __float_as_uint(c.w);
-  ps.L = v3(d.x, d.y, d.z);
-  ps.T = v3(d.w, e.x, e.y);
-  ps.sum = v3(e.z, e.w, f.x);
-  ps.rng.s = (uint64_t)__float_as_uint(f.y) | ((uint64_t)__float_as_uint(f.z) << 32);
-  ps.fog_mat = __float_as_uint(f.w);
+  ps.ray.dir = v3(a.w, b.w, d.x);
+  uint32_t meta = __float_as_uint(d.y);
+  ps.ray.zero_length = (meta & 1u) != 0u;
+  ps.depth = (meta >> 8) & 255u;
+  ps.fog_pending = (meta & 65536u) != 0u;
+  pixslot = __float_as_uint(d.z);
+  ps.s = __float_as_uint(d.w);
+  ps.L = v3(e.x, e.y, e.z);
+  ps.T = v3(e.w, f.x, f.y);
+  ps.rng.s = (uint64_t)__float_as_uint(f.z) | ((uint64_t)__float_as_uint(f.w) << 32);
+  ps.sum = v3(0.f, 0.f, 0.f);
   ps.fog_pos = v3(0.f, 0.f, 0.f);
+  ps.fog_mat = 0;
   if (ps.fog_pending) {
-    float4 g = p[6 * (size_t)B.cap];
+    float4 g = __ldcs(p + 5 * c);
     ps.fog_pos = v3(g.x, g.y, g.z);
+    ps.fog_mat = __float_as_uint(g.w);
   }
   h.param = hh.x;
   h.object = __float_as_uint(hh.y);
   h.prim = __float_as_uint(hh.z);
   h.u = hh.w;
-  h.v = hi.x;
+  h.v = hv;
 }
 
-__device__ __forceinline__ void wf_store_hit(const WfBuffers& B, uint32_t slot, const Hit& h) {
-  float4* p = B.planes + slot;
-  p[7 * (size_t)B.cap] = make_float4(h.param, __uint_as_float(h.object), __uint_as_float(h.prim), h.u);
-  p[8 * (size_t)B.cap] = make_float4(h.v, 0.f, 0.f, 0.f);
-}
-
-// Appends the slots of the lanes with `alive` to list_out: ballot + one atomic per warp.
-__device__ __forceinline__ void wf_append(const WfBuffers& B, bool alive, uint32_t slot) {
-  unsigned m = __ballot_sync(0xFFFFFFFFu, alive);
-  if (!m) return;
-  const int lane = threadIdx.x & 31;
-  const int leader = __ffs(m) - 1;
-  uint32_t base = 0;
-  if (lane == leader) base = atomicAdd(B.counters + 1, (uint32_t)__popc(m));
-  base = __shfl_sync(0xFFFFFFFFu, base, leader);
-  if (alive) B.list_out[base + __popc(m & ((1u << lane) - 1u))] = slot;
+__device__ __forceinline__ void wf_store_hit(const WfBuffers& B, uint32_t i, const Hit& h) {
+  __stcs(B.hit + i, make_float4(h.param, __uint_as_float(h.object), __uint_as_float(h.prim), h.u));
+  __stcs(B.hit_v + i, h.v);
 }
 
 // ------------------------------------------------------------------ kernels
-// (PathState, begin_path, finish_segment, film_add, warp_add: fs2_kernels.cuh, which
-// includes this file after defining them.)
+// (PathState, begin_path, shade_segment, warp_add: fs2_kernels.cuh, which includes this file
+// after defining them.)
 
-__global__ void __launch_bounds__(128)
-k_wf_begin(CamBasis cam, Film film, TraceParams tp, WfBuffers B) {
-  uint32_t slot = blockIdx.x * 128u + threadIdx.x;
-  int px, py;
-  wf_slot_pixel(B, slot, px, py);
-  bool mine = slot < B.cap && px < film.width && py < film.height && tp.n_samples > 0;
-  if (mine) {
-    PathState ps;
-    ps.sum = v3(0.f, 0.f, 0.f);
-    ps.s = 0;
-    ps.fog_mat = 0;
-    ps.fog_pos = v3(0.f, 0.f, 0.f);
-    begin_path(cam, tp, (uint32_t)(py * film.width + px), px, py, ps);
-    wf_store_path(B, slot, ps);
-  }
-  wf_append(B, mine, slot);
-}
-
-// n_in <- n_out, n_out <- 0, cursor <- 0; the lists are swapped by the host (pointer swap).
-__global__ void k_wf_flip(uint32_t* counters) {
-  counters[0] = counters[1];
+// n_in <- n_out, n_out <- 0, cursor <- 0, swap the state arrays; tells the host how many
+// paths the wave it starts has.
+__global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
+  uint32_t n = counters[1];
+  counters[0] = n;
   counters[1] = 0;
   counters[2] = 0;
+  counters[3] ^= 1u;
+  counters[6] += 1u;
+  *(volatile uint32_t*)host_live = n;
+  __threadfence_system();
 }
 
 template <bool STATS>
@@ -167,10 +160,14 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   const unsigned FULL = 0xFFFFFFFFu;
   const int lane = threadIdx.x & 31;
   const uint32_t n_in = B.counters[0];
+  const float4* st = B.state[B.counters[3] & 1u];
+  // small waves: spread the rays over all warps instead of 128 per warp
+  const uint32_t per_warp = n_in / (gridDim.x * (FS2_PH_THREADS / 32)) + 1u;
+  const uint32_t chunk = min((uint32_t)FS2_WF_CHUNK, (per_warp + 31u) & ~31u);
   Counters c = {0, 0, 0, 0, 0, 0};
   Ray ray = make_ray(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f));
   LbRay q = make_lbray(ray);
-  uint32_t slot = 0;
+  uint32_t idx = 0;
   PhLane w;
   w.st = PH_IDLE;
   w.rec = no_hit();
@@ -191,21 +188,21 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
     if (idle && ((uint32_t)__popc(idle) >= fetch_min || idle == FULL || exhausted)) {
       if (chunk_next == chunk_end && !exhausted) {
         uint32_t b = 0;
-        if (lane == 0) b = atomicAdd(B.counters + 2, (uint32_t)FS2_WF_CHUNK);
+        if (lane == 0) b = atomicAdd(B.counters + 2, chunk);
         b = __shfl_sync(FULL, b, 0);
         if (b >= n_in) {
           exhausted = true;
         } else {
           chunk_next = b;
-          chunk_end = min(b + (uint32_t)FS2_WF_CHUNK, n_in);
+          chunk_end = min(b + chunk, n_in);
         }
       }
       uint32_t avail = chunk_end - chunk_next;
       if (avail) {
         uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
         if (w.st == PH_IDLE && rank < avail) {
-          slot = B.list_in[chunk_next + rank];
-          ray = wf_load_ray(B, slot);
+          idx = chunk_next + rank;
+          ray = wf_load_ray(st, B.cap, idx);
           q = ph_segment_start(S, w, ray);
         }
         chunk_next += min((uint32_t)__popc(idle), avail);
@@ -219,7 +216,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
     FS2_PHASE(PH_LB_TRIS, 2, ph_lb_tris<STATS>(S, w, ray, sm, c))
     FS2_PHASE(PH_RETURN, 4, ph_return(S, w, ray, sm))
     if (w.st == PH_SHADE) {  // nearest hit of the segment is final
-      wf_store_hit(B, slot, w.rec);
+      wf_store_hit(B, idx, w.rec);
       w.st = PH_IDLE;
     }
   }
@@ -233,33 +230,82 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   }
 }
 
+// FRESH: fill the pool (every thread starts a path).  Otherwise: finish the traced segment of
+// live path `idx`, then continue it, or replace it by the next path id.
+template <bool FRESH>
 __global__ void __launch_bounds__(128)
 k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
            unsigned long long* __restrict__ stats) {
-  const uint32_t n_in = B.counters[0];
-  uint32_t idx = blockIdx.x * 128u + threadIdx.x;
-  if (blockIdx.x * 128u >= n_in) return;  // whole block past the live list
-  bool have = idx < n_in;
-  bool alive = false;
-  uint32_t slot = 0, n_shade = 0, finished = 0;
-  if (have) {
-    slot = B.list_in[idx];
-    int px, py;
-    wf_slot_pixel(B, slot, px, py);
-    const uint32_t pixel = (uint32_t)(py * film.width + px);
-    PathState ps;
+  const unsigned FULL = 0xFFFFFFFFu;
+  const uint32_t n_in = FRESH ? B.cap : B.counters[0];
+  if (blockIdx.x * 128u >= n_in) return;  // whole block past the live paths
+  const uint32_t cur = B.counters[3] & 1u;
+  const uint32_t idx = blockIdx.x * 128u + threadIdx.x;
+  const int lane = threadIdx.x & 31;
+  const bool have = idx < n_in;
+  bool alive = false, need = FRESH && have;
+  uint32_t n_shade = 0, finished = 0, pixslot = 0;
+  PathState ps;
+  ps.sum = v3(0.f, 0.f, 0.f);
+  ps.s = 0;
+  ps.fog_mat = 0;
+  ps.fog_pos = v3(0.f, 0.f, 0.f);
+  if (!FRESH && have) {
     Hit h;
-    wf_load_path(B, slot, ps, h);
-    uint32_t s_before = ps.s;
-    alive = finish_segment(S, cam, film, tp, pixel, px, py, ps, h, n_shade);
-    finished = ps.s - s_before;
-    if (alive) wf_store_path(B, slot, ps);
-    else film_add(film, pixel, ps.sum, tp.n_samples);
+    wf_load_path(B, B.state[cur], idx, ps, pixslot, h);
+    int px, py;
+    wf_slot_pixel(B, pixslot, px, py);
+    const uint32_t pixel = (uint32_t)(py * film.width + px);
+    if (shade_segment(S, cam, film, pixel, ps.s + 1 == tp.n_samples, ps, h, n_shade)) {
+      atomicAdd(film.sum + pixel, make_float4(ps.L.x, ps.L.y, ps.L.z, 1.0f));
+      finished = 1;
+      need = true;
+    } else {
+      alive = true;
+    }
   }
-  wf_append(B, alive, slot);
-  warp_add(stats + ST_PATHS, finished);
-  warp_add(stats + ST_SEGMENTS, have ? 1u : 0u);
-  warp_add(stats + ST_SHADE, n_shade);
+  // ---- regeneration: the lanes that need a path take consecutive ids (one atomic per warp)
+  for (;;) {
+    unsigned m = __ballot_sync(FULL, need);
+    if (!m) break;
+    const int leader = __ffs(m) - 1;
+    unsigned long long base = 0;
+    if (lane == leader)
+      base = atomicAdd((unsigned long long*)(B.counters + 4), (unsigned long long)__popc(m));
+    base = __shfl_sync(FULL, base, leader);
+    if (need) {
+      unsigned long long id = base + (unsigned)__popc(m & ((1u << lane) - 1u));
+      if (id >= B.total) {
+        need = false;  // no camera paths left
+      } else {
+        ps.s = (uint32_t)(id / B.pix_cap);
+        pixslot = (uint32_t)(id % B.pix_cap);
+        int px, py;
+        wf_slot_pixel(B, pixslot, px, py);
+        if (px < film.width && py < film.height) {  // else: padding pixel, take another id
+          begin_path(cam, tp, (uint32_t)(py * film.width + px), px, py, ps);
+          alive = true;
+          need = false;
+        }
+      }
+    }
+  }
+  // ---- compaction: live lanes write their state densely into the other array
+  unsigned ma = __ballot_sync(FULL, alive);
+  if (ma) {
+    const int leader = __ffs(ma) - 1;
+    uint32_t base = 0;
+    if (lane == leader) base = atomicAdd(B.counters + 1, (uint32_t)__popc(ma));
+    base = __shfl_sync(FULL, base, leader);
+    if (alive)
+      wf_store_path(B.state[cur ^ 1u], B.cap, base + (uint32_t)__popc(ma & ((1u << lane) - 1u)), ps,
+                    pixslot);
+  }
+  if (!FRESH) {
+    warp_add(stats + ST_PATHS, finished);
+    warp_add(stats + ST_SEGMENTS, have ? 1u : 0u);
+    warp_add(stats + ST_SHADE, n_shade);
+  }
 }
 
 }  // namespace fs2

@@ -99,9 +99,10 @@ def test_aux_buffers_match_oracle_without_jitter(ctx):
 
 def _variants_agree(ctx, scene, cam, w, h, spp):
     """default (leaf BVH, warp-synchronous phase machine), leaf BVH walked by free-running
-    lanes, the wavefront pipeline (separate trace / shade kernels, state in HBM), warp-cooperative linear scan and per-thread linear scan (the reference's loop
-    order) must produce identical hits: same seeds -> identical films, aux
-    buffers, ids and reference-equivalent work counters."""
+    lanes, the wavefront pipeline (separate trace / shade kernels, path pool in HBM),
+    warp-cooperative linear scan and per-thread linear scan (the reference's loop order) must
+    produce identical hits: same seeds -> identical films (wavefront: to summation order),
+    aux buffers, ids and reference-equivalent work counters."""
     import fs2_b200
     ctx.upload(scene)
     ctx.resize(w, h)
@@ -118,7 +119,12 @@ def _variants_agree(ctx, scene, cam, w, h, spp):
         assert sl[k] == sl2[k], k  # same rays, same reference-equivalent work
         assert sl[k] == sw[k], k
     for f in (fl, fl2, fw, fa):
-        assert (f["mean"].view(np.uint32) == fb["mean"].view(np.uint32)).all()
+        if f is fw:
+            # same paths, same radiance per path; the wavefront adds a pixel's samples to the
+            # film with float atomics, so only the summation order differs
+            assert np.allclose(f["mean"], fb["mean"], rtol=4e-7 * spp, atol=1e-7)
+        else:
+            assert (f["mean"].view(np.uint32) == fb["mean"].view(np.uint32)).all()
         assert (f["normal"].view(np.uint32) == fb["normal"].view(np.uint32)).all()
         assert (f["depth"].view(np.uint32) == fb["depth"].view(np.uint32)).all()
         assert (f["mat_id"] == fb["mat_id"]).all()
