@@ -274,7 +274,14 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   ctx->launches++;
   // every path has at most 8 segments and the pool is refilled every wave
   const unsigned long long max_waves = 8ull * ((total + cap - 1) / cap) + 8ull;
-  const int persistent = ctx->sm_count * 4;
+  const unsigned smem = ph_smem_bytes(ctx->ds.scene_root >= 0);
+  int per_sm = 0;
+  if (ctx->stats_build)
+    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_trace<true>, FS2_PH_THREADS, smem));
+  else
+    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_trace<false>, FS2_PH_THREADS, smem));
+  if (per_sm < 1) per_sm = 1;
+  const int persistent = ctx->sm_count * per_sm;  // one resident generation of CTAs
   const uint32_t shade_blocks = cap / 128u;
   for (unsigned long long wave = 0; wave < max_waves; wave++) {
     if (wave >= FS2_WF_AHEAD) {
@@ -284,10 +291,10 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
     k_wf_flip<<<1, 1, 0, ctx->stream>>>(B.counters, B.host_live);
     CUDA_TRY(ctx, cudaEventRecord(ctx->wf_events[wave % FS2_WF_AHEAD], ctx->stream));
     if (ctx->stats_build)
-      k_wf_trace<true><<<persistent, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(ctx->ds, B, tp,
+      k_wf_trace<true><<<persistent, FS2_PH_THREADS, smem, ctx->stream>>>(ctx->ds, B, tp,
                                                                                      ctx->d_stats);
     else
-      k_wf_trace<false><<<persistent, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(ctx->ds, B, tp,
+      k_wf_trace<false><<<persistent, FS2_PH_THREADS, smem, ctx->stream>>>(ctx->ds, B, tp,
                                                                                       ctx->d_stats);
     k_wf_shade<false><<<shade_blocks, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
     ctx->launches += 3;
@@ -581,10 +588,10 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
       if (st) FS2_LAUNCH((k_trace_mega<true, true>)); else FS2_LAUNCH((k_trace_mega<false, true>));
     } else {
       if (st)
-        k_trace_phase<true><<<grid, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(
+        k_trace_phase<true><<<grid, FS2_PH_THREADS, ph_smem_bytes(ctx->ds.scene_root >= 0), ctx->stream>>>(
             ctx->ds, cb, film, tp, ctx->d_stats);
       else
-        k_trace_phase<false><<<grid, FS2_PH_THREADS, FS2_PH_SMEM_BYTES, ctx->stream>>>(
+        k_trace_phase<false><<<grid, FS2_PH_THREADS, ph_smem_bytes(ctx->ds.scene_root >= 0), ctx->stream>>>(
             ctx->ds, cb, film, tp, ctx->d_stats);
     }
 #undef FS2_LAUNCH

@@ -345,7 +345,7 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
   w.obj_i = w.cur_obj = w.sleaf_first = w.sleaf_count = w.sleaf_i = w.cur = 0;
   w.msp = w.ssp = 0;
   w.flags = 0;
-  w.lb_cur = 0;
+  w.lb_cur = w.lb_root = 0;
   w.lb_sp = 0;
   w.bt = w.bu = w.bv = 0.f;
   w.border = w.qbase = w.qcount = w.qmask = 0;

@@ -16,8 +16,13 @@
 // are bit-identical (tests/test_gpu_image.py compares all variants).
 //
 // Per-lane stacks live in shared memory, one 4-byte column per thread (conflict-free):
-//   octree frames   (FS2_PH_MESH_FRAMES + FS2_PH_SCENE_FRAMES) x 8 words
-//   leaf-BVH stack  FS2_PH_LB_STACK x 2 words
+//   mesh-octree frames   FS2_PH_MESH_FRAMES x 8 words
+//   leaf-BVH stack       FS2_PH_LB_STACK x 1 word: (node - leaf root) << 16 | bf16(entry t),
+//                        a leaf's tree has < 65 536 nodes (fs2_lbvh_build.h) and a truncated
+//                        entry parameter only makes the pop-time cull conservative
+//   scene-octree frames  FS2_PH_SCENE_FRAMES x 8 words, allocated only when the scene has a
+//                        tree (>= 182 objects): 200 B instead of 360 B per lane otherwise, which
+//                        is what bounds the CTAs per SM (and what is left for L1)
 #pragma once
 #include "fs2_shade.cuh"
 
@@ -27,8 +32,13 @@ namespace fs2 {
 #define FS2_PH_MESH_FRAMES 4   // mesh trees: internal nodes at depth 0..3 (mesh.cpp:16)
 #define FS2_PH_SCENE_FRAMES 5  // scene trees: internal nodes at depth 0..4 (<= ~2 M objects)
 #define FS2_PH_LB_STACK 18     // 6 inner leaf-BVH levels x 3 pending siblings
-#define FS2_PH_SLOTS ((FS2_PH_MESH_FRAMES + FS2_PH_SCENE_FRAMES) * 8 + FS2_PH_LB_STACK * 2)
+#define FS2_PH_SLOTS_NOTREE (FS2_PH_MESH_FRAMES * 8 + FS2_PH_LB_STACK)
+#define FS2_PH_SLOTS (FS2_PH_SLOTS_NOTREE + FS2_PH_SCENE_FRAMES * 8)
 #define FS2_PH_SMEM_BYTES (FS2_PH_SLOTS * FS2_PH_THREADS * 4)
+// dynamic shared memory of a phase-machine kernel for a scene with / without a scene tree
+static inline unsigned ph_smem_bytes(bool scene_tree) {
+  return (scene_tree ? FS2_PH_SLOTS : FS2_PH_SLOTS_NOTREE) * FS2_PH_THREADS * 4u;
+}
 
 #ifndef FS2_PH_SHADE_BATCH
 #define FS2_PH_SHADE_BATCH 8   // shade when this many lanes wait (or nothing else can run)
@@ -59,7 +69,7 @@ struct PhLane {
   int msp, ssp;                                // frame counts of the mesh / scene walk
   uint32_t flags;                              // bit0 walking a mesh tree, bit1 ret, bit2 scene leaf improved
   // leaf BVH walk
-  uint32_t lb_cur;
+  uint32_t lb_cur, lb_root;
   int lb_sp;
   float bt, bu, bv;
   uint32_t border;
@@ -78,13 +88,11 @@ struct PhSmem {
   __device__ __forceinline__ float& f(int slot) const {
     return reinterpret_cast<float*>(col)[slot * FS2_PH_THREADS];
   }
-  // frame k (mesh frames first, then scene frames), word i
+  // word i of frame sp: mesh frames first, then the leaf-BVH stack, scene frames last
   __device__ __forceinline__ int fslot(bool mesh, int sp, int i) const {
-    return ((mesh ? 0 : FS2_PH_MESH_FRAMES) + sp) * 8 + i;
+    return (mesh ? 0 : FS2_PH_SLOTS_NOTREE) + sp * 8 + i;
   }
-  __device__ __forceinline__ int lslot(int sp, int i) const {
-    return (FS2_PH_MESH_FRAMES + FS2_PH_SCENE_FRAMES) * 8 + sp * 2 + i;
-  }
+  __device__ __forceinline__ int lslot(int sp) const { return FS2_PH_MESH_FRAMES * 8 + sp; }
 };
 
 // frame words: 0 node, 1 bits, 2..4 tx ty tz, 5..7 sx sy sz   (struct Frame, fs2_traverse.cuh)
@@ -149,6 +157,7 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
         w.border = 0;
         w.flags &= ~PH_F_FOUND;
         w.lb_sp = 0;
+        w.lb_root = root;
         if (root == 0xFFFFFFFFu) {
           w.qbase = n.first;
           w.qcount = n.count;
@@ -319,9 +328,9 @@ __device__ __forceinline__ void ph_leaf_done(PhLane& w) {
 __device__ __forceinline__ void ph_lb_pop(PhLane& w, const PhSmem& sm) {
   while (w.lb_sp > 0) {
     --w.lb_sp;
-    float te = sm.f(sm.lslot(w.lb_sp, 1));
-    if (te <= fminf(w.bt, 1.0f)) {
-      w.lb_cur = sm.w(sm.lslot(w.lb_sp, 0));
+    uint32_t e = sm.w(sm.lslot(w.lb_sp));
+    if (__uint_as_float(e << 16) <= fminf(w.bt, 1.0f)) {
+      w.lb_cur = w.lb_root + (e >> 16);
       w.st = PH_LB_NODE;
       return;
     }
@@ -373,18 +382,15 @@ __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray
   FS2_CSWAP(t1, c1, t2, c2)
 #undef FS2_CSWAP
   if (t3 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
-    sm.w(sm.lslot(w.lb_sp, 0)) = c3;
-    sm.f(sm.lslot(w.lb_sp, 1)) = t3;
+    sm.w(sm.lslot(w.lb_sp)) = ((c3 - w.lb_root) << 16) | (__float_as_uint(t3) >> 16);
     w.lb_sp++;
   }
   if (t2 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
-    sm.w(sm.lslot(w.lb_sp, 0)) = c2;
-    sm.f(sm.lslot(w.lb_sp, 1)) = t2;
+    sm.w(sm.lslot(w.lb_sp)) = ((c2 - w.lb_root) << 16) | (__float_as_uint(t2) >> 16);
     w.lb_sp++;
   }
   if (t1 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
-    sm.w(sm.lslot(w.lb_sp, 0)) = c1;
-    sm.f(sm.lslot(w.lb_sp, 1)) = t1;
+    sm.w(sm.lslot(w.lb_sp)) = ((c1 - w.lb_root) << 16) | (__float_as_uint(t1) >> 16);
     w.lb_sp++;
   }
   if (t0 < 3.0f) {

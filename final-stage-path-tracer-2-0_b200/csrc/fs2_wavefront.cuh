@@ -151,8 +151,11 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
   __threadfence_system();
 }
 
+#ifndef FS2_WF_MIN_BLOCKS
+#define FS2_WF_MIN_BLOCKS 6
+#endif
 template <bool STATS>
-__global__ void __launch_bounds__(FS2_PH_THREADS, 4)
+__global__ void __launch_bounds__(FS2_PH_THREADS, FS2_WF_MIN_BLOCKS)
 k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict__ stats) {
   extern __shared__ uint32_t ph_smem[];
   PhSmem sm;
@@ -175,7 +178,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   w.obj_i = w.cur_obj = w.sleaf_first = w.sleaf_count = w.sleaf_i = w.cur = 0;
   w.msp = w.ssp = 0;
   w.flags = 0;
-  w.lb_cur = 0;
+  w.lb_cur = w.lb_root = 0;
   w.lb_sp = 0;
   w.bt = w.bu = w.bv = 0.f;
   w.border = w.qbase = w.qcount = w.qmask = 0;
