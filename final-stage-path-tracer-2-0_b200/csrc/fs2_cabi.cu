@@ -57,7 +57,7 @@ struct fs_ctx {
   uint64_t launches = 0;
   float last_trace_ms = 0.f, last_kernel_ms = 0.f;
   bool stats_build = false;
-  uint32_t tune = 2;  // FS2_TUNE
+  uint32_t tune = 8;  // FS2_TUNE: bits 0-4 idle lanes that trigger a refill in k_wf_trace, bits 8.. pool size (1024 paths)
 };
 
 namespace {

@@ -89,6 +89,69 @@ __device__ __forceinline__ void lb_test_tris(const DScene& S, uint32_t k0, uint3
   }
 }
 
+// L2 -> L1 prefetch hint: the phase machine knows a lane's next node / triangle group one
+// loop iteration before it reads it, and other lanes' phases run in between.
+__device__ __forceinline__ void prefetch_l1(const void* p) {
+  asm volatile("prefetch.global.L1 [%0];" ::"l"(p));
+}
+
+// lb_test_tris for one group of n <= 4 records, restructured for memory-level parallelism:
+// the four planes are fetched together and the plane stage runs on all of them before the
+// (sequential, order-dependent) acceptance stage; the barycentric constants of the records
+// that pass the plane stage are prefetched while the others are still being looked at.
+// Same float expressions and the same acceptance order as lb_test_tris.
+template <bool STATS>
+__device__ __forceinline__ void lb_test_group(const DScene& S, uint32_t k0, uint32_t n, V3 s, V3 d,
+                                              float& bt, uint32_t& border, bool& found, float& bu,
+                                              float& bv, Counters& c) {
+  if (STATS) c.n_tritest += n;
+  float tt[4];
+  unsigned cand = 0;
+  {
+    float4 pl[4];
+#pragma unroll
+    for (uint32_t j = 0; j < 4; j++) pl[j] = __ldg(S.lb_plane + k0 + (j < n ? j : n - 1u));
+#pragma unroll
+    for (uint32_t j = 0; j < 4; j++) {
+      float ts = pl[j].x * d.x + pl[j].y * d.y + pl[j].z * d.z;
+      float ns = -(pl[j].x * s.x + pl[j].y * s.y + pl[j].z * s.z + pl[j].w);
+      bool ok = j < n && !near_zero(ts);
+      float t = ns / (ok ? ts : 1.0f);
+      ok = ok && t >= 0.0f && t <= 1.0f && !(t > bt);
+      tt[j] = t;
+      if (ok) {
+        cand |= 1u << j;
+        prefetch_l1(S.lb_aux + 3 * (size_t)(k0 + j));
+      }
+    }
+  }
+#pragma unroll 1
+  while (cand) {
+    uint32_t j = (uint32_t)__ffs((int)cand) - 1u;
+    cand &= cand - 1u;
+    float t = j == 0u ? tt[0] : j == 1u ? tt[1] : j == 2u ? tt[2] : tt[3];
+    uint32_t k = k0 + j;
+    uint32_t ord = 0;
+    if (!(t < bt)) {
+      // equal parameters: the sequential loop keeps the record it met first
+      if (!(t == bt) || !found) continue;
+      ord = __ldg(S.lb_order + k);
+      if (!(ord < border)) continue;
+    } else {
+      ord = __ldg(S.lb_order + k);
+    }
+    float u, v;
+    if (STATS) c.n_bary++;
+    if (tri_inside(S.lb_aux + 3 * (size_t)k, s + d * t, u, v)) {
+      bt = t;
+      border = ord;
+      found = true;
+      bu = u;
+      bv = v;
+    }
+  }
+}
+
 // Leaf query.  `stack` is this lane's column of a shared-memory stack (stride
 // FS2_LB_THREADS entries).  Returns true when the leaf improved `h`.
 template <bool STATS>

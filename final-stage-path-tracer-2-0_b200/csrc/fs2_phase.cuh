@@ -147,8 +147,10 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
       uint32_t root = __ldg(&S.lb_leaf[w.cur].x);
       if (r.zero_length || (root == 0xFFFFFFFFu && n.count > 16u)) {
         // rare: point query / leaf beyond the BVH level cap -> linear scan in reference order
-        bool ret = mesh_leaf_cold<STATS>(S, n.first, n.count, r, w.cur_obj, w.rec, c);
-        w.flags = ret ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
+        ColdResult cr = mesh_leaf_cold<STATS>(S, n.first, n.count, r, w.cur_obj, w.rec, c);
+        w.rec = cr.h;
+        c = cr.c;
+        w.flags = cr.ret ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
         w.st = PH_RETURN;
       } else {
         if (STATS) c.n_tri += n.count;
@@ -162,9 +164,11 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
           w.qbase = n.first;
           w.qcount = n.count;
           w.qmask = (1u << ((n.count + 3u) >> 2)) - 1u;
+          prefetch_l1(S.lb_plane + n.first);
           w.st = PH_LB_TRIS;
         } else {
           w.lb_cur = root;
+          prefetch_l1(S.lb_nodes + 8 * (size_t)root);
           w.st = PH_LB_NODE;
         }
       }
@@ -192,6 +196,7 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
   sm.f(sm.fslot(mesh, sp, 7)) = st.z;
   sp++;
   w.cur = n.first + bits;
+  prefetch_l1(S.nodes + 2 * (size_t)w.cur);
   // stays in PH_ENTER
 }
 
@@ -262,6 +267,7 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
   bits = ((bits ^ flip) & ~(3u << 3)) | (visits << 3);
   sm.w(sm.fslot(mesh, f, 1)) = bits;
   w.cur = pn.first + (bits & 7u);
+  prefetch_l1(S.nodes + 2 * (size_t)w.cur);
   w.st = PH_ENTER;
 }
 
@@ -295,6 +301,7 @@ __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray&
     if (root != 0xFFFFFFFFu) {
       w.cur_obj = oi;
       w.cur = root;
+      prefetch_l1(S.nodes + 2 * (size_t)root);
       w.msp = 0;
       w.flags |= PH_F_MESH;
       w.st = PH_ENTER;
@@ -325,12 +332,13 @@ __device__ __forceinline__ void ph_leaf_done(PhLane& w) {
 }
 
 // Next pending leaf-BVH node that can still matter, or leaf done.
-__device__ __forceinline__ void ph_lb_pop(PhLane& w, const PhSmem& sm) {
+__device__ __forceinline__ void ph_lb_pop(PhLane& w, const DScene& S, const PhSmem& sm) {
   while (w.lb_sp > 0) {
     --w.lb_sp;
     uint32_t e = sm.w(sm.lslot(w.lb_sp));
     if (__uint_as_float(e << 16) <= fminf(w.bt, 1.0f)) {
       w.lb_cur = w.lb_root + (e >> 16);
+      prefetch_l1(S.lb_nodes + 8 * (size_t)w.lb_cur);
       w.st = PH_LB_NODE;
       return;
     }
@@ -359,9 +367,10 @@ __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray
       w.qbase = meta.x;
       w.qcount = meta.z;
       w.qmask = mask;
+      prefetch_l1(S.lb_plane + meta.x + 4u * ((uint32_t)__ffs((int)mask) - 1u));
       w.st = PH_LB_TRIS;
     } else {
-      ph_lb_pop(w, sm);
+      ph_lb_pop(w, S, sm);
     }
     return;
   }
@@ -395,9 +404,10 @@ __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray
   }
   if (t0 < 3.0f) {
     w.lb_cur = c0;  // stays in PH_LB_NODE
+    prefetch_l1(S.lb_nodes + 8 * (size_t)c0);
     return;
   }
-  ph_lb_pop(w, sm);
+  ph_lb_pop(w, S, sm);
 }
 
 template <bool STATS>
@@ -407,10 +417,11 @@ __device__ __forceinline__ void ph_lb_tris(const DScene& S, PhLane& w, const Ray
   w.qmask &= w.qmask - 1u;
   uint32_t rem = w.qcount - 4u * g;
   bool found = (w.flags & PH_F_FOUND) != 0;
-  lb_test_tris<STATS>(S, w.qbase + 4u * g, rem < 4u ? rem : 4u, r.start, r.dir, w.bt, w.border,
-                      found, w.bu, w.bv, c);
+  if (w.qmask) prefetch_l1(S.lb_plane + w.qbase + 4u * ((uint32_t)__ffs((int)w.qmask) - 1u));
+  lb_test_group<STATS>(S, w.qbase + 4u * g, rem < 4u ? rem : 4u, r.start, r.dir, w.bt, w.border,
+                       found, w.bu, w.bv, c);
   if (found) w.flags |= PH_F_FOUND;
-  if (!w.qmask) ph_lb_pop(w, sm);
+  if (!w.qmask) ph_lb_pop(w, S, sm);
 }
 
 }  // namespace fs2

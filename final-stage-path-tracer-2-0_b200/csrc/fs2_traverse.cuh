@@ -211,11 +211,22 @@ __device__ __forceinline__ bool mesh_leaf(const DScene& S, uint32_t first, uint3
 namespace fs2 {
 
 // Out-of-line copy for the rare callers inside the phase machine (zero-length rays, leaves
-// beyond the leaf-BVH level cap).
+// beyond the leaf-BVH level cap).  Everything goes in and out by value: a reference
+// parameter would pin the caller's ray / record / scene descriptor in local memory for the
+// whole kernel (ncu: 5 % of the traversal kernel's instructions were LDL/STL).
+struct ColdResult {
+  Hit h;
+  Counters c;
+  bool ret;
+};
 template <bool STATS>
-__device__ __noinline__ bool mesh_leaf_cold(const DScene& S, uint32_t first, uint32_t count,
-                                            const Ray& r, uint32_t object, Hit& h, Counters& c) {
-  return mesh_leaf<STATS>(S, first, count, r, object, h, c);
+__device__ __noinline__ ColdResult mesh_leaf_cold(DScene S, uint32_t first, uint32_t count, Ray r,
+                                                  uint32_t object, Hit h, Counters c) {
+  ColdResult o;
+  o.h = h;
+  o.c = c;
+  o.ret = mesh_leaf<STATS>(S, first, count, r, object, o.h, o.c);
+  return o;
 }
 
 // ------------------------------------------------------------------ octree walker

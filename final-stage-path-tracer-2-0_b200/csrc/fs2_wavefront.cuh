@@ -152,7 +152,7 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 }
 
 #ifndef FS2_WF_MIN_BLOCKS
-#define FS2_WF_MIN_BLOCKS 6
+#define FS2_WF_MIN_BLOCKS 5  // measured: 4 -> 262, 5 -> 294, 6 -> 287 (64 B of spills), 8 -> 268 Mpaths/s
 #endif
 template <bool STATS>
 __global__ void __launch_bounds__(FS2_PH_THREADS, FS2_WF_MIN_BLOCKS)

@@ -46,6 +46,8 @@ def load_library(path=None):
     if _lib is not None and path is None:
         return _lib
     if path is None:
+        path = os.environ.get("FS2_CUDA_LIB")  # experiments: an alternative build of the same ABI
+    if path is None:
         path = build.CUDA_LIB
         if not os.path.exists(path):
             build.build_cuda()
