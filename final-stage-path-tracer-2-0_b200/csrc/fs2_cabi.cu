@@ -32,6 +32,9 @@ struct DeviceBuf {
 
 }  // namespace
 
+#define FS2_WF_AHEAD 4  // waves kept enqueued per pipe
+#define FS2_WF_PIPES 2  // independent halves of the path pool (two streams)
+
 struct fs_ctx {
   int device = 0;
   cudaStream_t stream = nullptr;      // stream in use
@@ -49,8 +52,10 @@ struct fs_ctx {
   int width = 0, height = 0;
   DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch;
   DeviceBuf wf_planes, wf_hit, wf_counters;  // wavefront path state
-  uint32_t* wf_host_live = nullptr;   // pinned: live paths of the newest wave
-  cudaEvent_t wf_events[4] = {};
+  uint32_t* wf_host_live = nullptr;   // pinned: live paths of the newest wave, per pipe
+  cudaEvent_t wf_events[FS2_WF_AHEAD * FS2_WF_PIPES] = {};
+  cudaStream_t wf_stream = nullptr;   // second pipe
+  cudaEvent_t wf_fork = nullptr, wf_join = nullptr;
   int sm_count = 148;
   // stats
   unsigned long long* d_stats = nullptr;
@@ -236,44 +241,63 @@ int collect_timing(fs_ctx* ctx) {
 }
 
 // Wavefront pipeline (fs2_wavefront.cuh): fill the pool, then per wave k_wf_flip / k_wf_trace /
-// k_wf_shade until no path is live.  The host never drains the stream: k_wf_flip publishes the
-// live count of the wave it starts in a pinned host word, the host keeps FS2_WF_AHEAD waves
-// enqueued (event ring) and stops enqueueing once a wave reported zero live paths; the waves
-// already in the queue then exit at once.
-#define FS2_WF_AHEAD 4
+// k_wf_shade until no path is live.
+//  * The pool is split into FS2_WF_PIPES independent halves on two streams that draw path ids
+//    from one counter: while the persistent traversal kernel of one half drains (its last
+//    warps finish their rays), the CTAs of the other half's kernel take over the SMs that
+//    become free, so the tail of every wave is overlapped instead of idling the machine.
+//  * The host never drains a stream: k_wf_flip publishes the live count of the wave it starts
+//    in a pinned host word, the host keeps FS2_WF_AHEAD waves enqueued per pipe (event ring)
+//    and stops enqueueing once a wave reported zero live paths; the waves already in the
+//    queue then exit at once.
 int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
   const uint32_t tiles_x = (uint32_t)(film.width + 15) / 16, tiles_y = (uint32_t)(film.height + 7) / 8;
   const uint32_t pix_cap = tiles_x * tiles_y * 128u;
   const unsigned long long total = (unsigned long long)pix_cap * tp.n_samples;
-  uint32_t cap = FS2_WF_MAX_PATHS;
-  if (ctx->tune >> 8) cap = (ctx->tune >> 8) << 10;  // FS2_TUNE bits 8..: pool size in 1024 paths
-  if ((unsigned long long)cap > total) cap = (uint32_t)((total + 127u) & ~127ull);
+  unsigned long long pool = FS2_WF_MAX_PATHS;
+  if (ctx->tune >> 8) pool = (unsigned long long)(ctx->tune >> 8) << 10;  // FS2_TUNE bits 8..
+  if (pool > total) pool = total;
+  int pipes = (ctx->tune & 32u) || pool < (1u << 18) ? 1 : FS2_WF_PIPES;  // FS2_TUNE bit 5: one pipe
+  const uint32_t cap = (uint32_t)(((pool + pipes - 1) / pipes + 127u) & ~127ull);
   int rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * FS2_WF_PLANES * 16 * 2))) return rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_hit, (size_t)cap * 20))) return rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_counters, 64))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * pipes * FS2_WF_PLANES * 16 * 2))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_hit, (size_t)cap * pipes * 20))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_counters, 64 * (FS2_WF_PIPES + 1)))) return rc;
   if (!ctx->wf_host_live) {
     CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->wf_host_live, 64, cudaHostAllocMapped));
-    for (int i = 0; i < FS2_WF_AHEAD; i++)
+    for (int i = 0; i < FS2_WF_AHEAD * FS2_WF_PIPES; i++)
       CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_events[i], cudaEventDisableTiming));
+    CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->wf_stream, cudaStreamNonBlocking));
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_fork, cudaEventDisableTiming));
+    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_join, cudaEventDisableTiming));
   }
-  WfBuffers B;
-  B.state[0] = (float4*)ctx->wf_planes.p;
-  B.state[1] = B.state[0] + (size_t)cap * FS2_WF_PLANES;
-  B.hit = (float4*)ctx->wf_hit.p;
-  B.hit_v = (float*)(B.hit + cap);
-  B.counters = (uint32_t*)ctx->wf_counters.p;
-  B.host_live = ctx->wf_host_live;
-  B.cap = cap;
-  B.pix_cap = pix_cap;
-  B.tiles_x = tiles_x;
-  B.total = total;
-  *(volatile uint32_t*)ctx->wf_host_live = 1u;
-  CUDA_TRY(ctx, cudaMemsetAsync(B.counters, 0, 64, ctx->stream));
-  k_wf_shade<true><<<cap / 128u, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
-  ctx->launches++;
+  WfBuffers B[FS2_WF_PIPES];
+  cudaStream_t streams[FS2_WF_PIPES];
+  for (int p = 0; p < pipes; p++) {
+    B[p].state[0] = (float4*)ctx->wf_planes.p + (size_t)p * 2 * cap * FS2_WF_PLANES;
+    B[p].state[1] = B[p].state[0] + (size_t)cap * FS2_WF_PLANES;
+    B[p].hit = (float4*)((char*)ctx->wf_hit.p + (size_t)p * cap * 20);
+    B[p].hit_v = (float*)(B[p].hit + cap);
+    B[p].counters = (uint32_t*)ctx->wf_counters.p + 16 * (p + 1);
+    B[p].next_path = (unsigned long long*)ctx->wf_counters.p;
+    B[p].host_live = ctx->wf_host_live + p;
+    B[p].cap = cap;
+    B[p].pix_cap = pix_cap;
+    B[p].tiles_x = tiles_x;
+    B[p].total = total;
+    streams[p] = p == 0 ? ctx->stream : ctx->wf_stream;
+    *(volatile uint32_t*)(ctx->wf_host_live + p) = 1u;
+  }
+  CUDA_TRY(ctx, cudaMemsetAsync(ctx->wf_counters.p, 0, 64 * (FS2_WF_PIPES + 1), ctx->stream));
+  if (pipes > 1) {
+    CUDA_TRY(ctx, cudaEventRecord(ctx->wf_fork, ctx->stream));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->wf_stream, ctx->wf_fork, 0));
+  }
+  for (int p = 0; p < pipes; p++)
+    k_wf_shade<true><<<cap / 128u, 128, 0, streams[p]>>>(ctx->ds, cb, film, tp, B[p], ctx->d_stats);
+  ctx->launches += pipes;
   // every path has at most 8 segments and the pool is refilled every wave
-  const unsigned long long max_waves = 8ull * ((total + cap - 1) / cap) + 8ull;
+  const unsigned long long max_waves = 8ull * ((total + pool - 1) / pool) + 8ull;
   const unsigned smem = ph_smem_bytes(ctx->ds.scene_root >= 0);
   int per_sm = 0;
   if (ctx->stats_build)
@@ -283,21 +307,34 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   if (per_sm < 1) per_sm = 1;
   const int persistent = ctx->sm_count * per_sm;  // one resident generation of CTAs
   const uint32_t shade_blocks = cap / 128u;
+  bool done[FS2_WF_PIPES] = {};
   for (unsigned long long wave = 0; wave < max_waves; wave++) {
-    if (wave >= FS2_WF_AHEAD) {
-      CUDA_TRY(ctx, cudaEventSynchronize(ctx->wf_events[wave % FS2_WF_AHEAD]));
-      if (*(volatile uint32_t*)ctx->wf_host_live == 0u) break;
+    int running = 0;
+    for (int p = 0; p < pipes; p++) {
+      if (done[p]) continue;
+      cudaEvent_t ev = ctx->wf_events[p * FS2_WF_AHEAD + wave % FS2_WF_AHEAD];
+      if (wave >= FS2_WF_AHEAD) {
+        CUDA_TRY(ctx, cudaEventSynchronize(ev));
+        if (*(volatile uint32_t*)(ctx->wf_host_live + p) == 0u) {
+          done[p] = true;
+          continue;
+        }
+      }
+      running++;
+      k_wf_flip<<<1, 1, 0, streams[p]>>>(B[p].counters, B[p].host_live);
+      CUDA_TRY(ctx, cudaEventRecord(ev, streams[p]));
+      if (ctx->stats_build)
+        k_wf_trace<true><<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
+      else
+        k_wf_trace<false><<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
+      k_wf_shade<false><<<shade_blocks, 128, 0, streams[p]>>>(ctx->ds, cb, film, tp, B[p], ctx->d_stats);
+      ctx->launches += 3;
     }
-    k_wf_flip<<<1, 1, 0, ctx->stream>>>(B.counters, B.host_live);
-    CUDA_TRY(ctx, cudaEventRecord(ctx->wf_events[wave % FS2_WF_AHEAD], ctx->stream));
-    if (ctx->stats_build)
-      k_wf_trace<true><<<persistent, FS2_PH_THREADS, smem, ctx->stream>>>(ctx->ds, B, tp,
-                                                                                     ctx->d_stats);
-    else
-      k_wf_trace<false><<<persistent, FS2_PH_THREADS, smem, ctx->stream>>>(ctx->ds, B, tp,
-                                                                                      ctx->d_stats);
-    k_wf_shade<false><<<shade_blocks, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, B, ctx->d_stats);
-    ctx->launches += 3;
+    if (!running) break;
+  }
+  if (pipes > 1) {
+    CUDA_TRY(ctx, cudaEventRecord(ctx->wf_join, ctx->wf_stream));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->wf_join, 0));
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return FS_OK;
@@ -374,6 +411,9 @@ int fs_destroy(fs_ctx* ctx) {
   if (ctx->wf_host_live) {
     cudaFreeHost(ctx->wf_host_live);
     for (cudaEvent_t e : ctx->wf_events) cudaEventDestroy(e);
+    if (ctx->wf_stream) cudaStreamDestroy(ctx->wf_stream);
+    if (ctx->wf_fork) cudaEventDestroy(ctx->wf_fork);
+    if (ctx->wf_join) cudaEventDestroy(ctx->wf_join);
   }
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);

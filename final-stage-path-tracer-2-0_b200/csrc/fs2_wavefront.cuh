@@ -37,15 +37,20 @@ namespace fs2 {
 
 #define FS2_WF_PLANES 6          // float4 planes of per-path state
 #define FS2_WF_CHUNK 128         // most ray indices a warp reserves per atomic
-#define FS2_WF_MAX_PATHS (1u << 22)  // pool size bound (state: 2 x 96 B + 20 B per path)
+#define FS2_WF_MAX_PATHS (1u << 23)  // pool size bound (state: 2 x 96 B + 20 B per path = 1.8 GB)
 
-// counters (uint32): 0 n_in, 1 n_out, 2 fetch cursor of k_wf_trace, 3 current state array,
-//                    4-5 next path id (uint64), 6 waves run
+// counters (uint32): 0 continuing paths of this wave, 1 continuing paths of the next wave,
+//                    2 fetch cursor of k_wf_trace, 3 current state array, 6 waves run,
+//                    7 new camera paths of the next wave, 8 new camera paths of this wave
+// A wave's array holds the continuing (bounce) paths from the front and the camera paths
+// started by the last shade kernel from the back, so warps of k_wf_trace pull either
+// coherent camera rays or bounce rays, not a mix of both.
 struct WfBuffers {
   float4* state[2];   // [FS2_WF_PLANES][cap], ping-pong
   float4* hit;        // [cap] param, object, prim, u   (same index as the ray of this wave)
   float* hit_v;       // [cap]
   uint32_t* counters;
+  unsigned long long* next_path;  // next path id; shared by the pipelines of one fs_trace
   uint32_t* host_live;  // pinned host word: live paths at the start of the newest wave
   uint32_t cap;         // paths in flight
   uint32_t pix_cap;     // pixel slots = padded 16x8 tiles x 128
@@ -64,6 +69,11 @@ __device__ __forceinline__ void wf_slot_pixel(const WfBuffers& B, uint32_t slot,
   uint32_t lane = t & 31u, warp = t >> 5;
   px = (int)((block % B.tiles_x) * 16u + (warp & 1u) * 8u + (lane & 7u));
   py = (int)((block / B.tiles_x) * 8u + (warp >> 1) * 4u + (lane >> 3));
+}
+
+// physical index of the i-th path of a wave with n_sec continuing paths
+__device__ __forceinline__ uint32_t wf_phys(uint32_t i, uint32_t n_sec, uint32_t cap) {
+  return i < n_sec ? i : cap - 1u - (i - n_sec);
 }
 
 __device__ __forceinline__ void wf_store_path(float4* st, uint32_t cap, uint32_t i,
@@ -138,16 +148,18 @@ __device__ __forceinline__ void wf_store_hit(const WfBuffers& B, uint32_t i, con
 // (PathState, begin_path, shade_segment, warp_add: fs2_kernels.cuh, which includes this file
 // after defining them.)
 
-// n_in <- n_out, n_out <- 0, cursor <- 0, swap the state arrays; tells the host how many
-// paths the wave it starts has.
+// next wave's counts become this wave's, cursor <- 0, swap the state arrays; tells the host how
+// many paths the wave it starts has.
 __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
-  uint32_t n = counters[1];
-  counters[0] = n;
+  uint32_t n_sec = counters[1], n_pri = counters[7];
+  counters[0] = n_sec;
+  counters[8] = n_pri;
   counters[1] = 0;
+  counters[7] = 0;
   counters[2] = 0;
   counters[3] ^= 1u;
   counters[6] += 1u;
-  *(volatile uint32_t*)host_live = n;
+  *(volatile uint32_t*)host_live = n_sec + n_pri;
   __threadfence_system();
 }
 
@@ -162,11 +174,10 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   sm.col = ph_smem + threadIdx.x;
   const unsigned FULL = 0xFFFFFFFFu;
   const int lane = threadIdx.x & 31;
-  const uint32_t n_in = B.counters[0];
+  const uint32_t n_sec = B.counters[0];
+  const uint32_t n_in = n_sec + B.counters[8];
   const float4* st = B.state[B.counters[3] & 1u];
-  // small waves: spread the rays over all warps instead of 128 per warp
-  const uint32_t per_warp = n_in / (gridDim.x * (FS2_PH_THREADS / 32)) + 1u;
-  const uint32_t chunk = min((uint32_t)FS2_WF_CHUNK, (per_warp + 31u) & ~31u);
+  const uint32_t n_warps = gridDim.x * (FS2_PH_THREADS / 32);
   Counters c = {0, 0, 0, 0, 0, 0};
   Ray ray = make_ray(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f));
   LbRay q = make_lbray(ray);
@@ -190,9 +201,17 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
     unsigned idle = __ballot_sync(FULL, w.st == PH_IDLE);
     if (idle && ((uint32_t)__popc(idle) >= fetch_min || idle == FULL || exhausted)) {
       if (chunk_next == chunk_end && !exhausted) {
-        uint32_t b = 0;
-        if (lane == 0) b = atomicAdd(B.counters + 2, chunk);
+        // guided self-scheduling: chunks shrink with the rays that are left, so the wave does
+        // not end with a few warps still holding 128 rays each
+        uint32_t b = 0, chunk = 0;
+        if (lane == 0) {
+          uint32_t seen = *(volatile uint32_t*)(B.counters + 2);
+          uint32_t left = seen < n_in ? n_in - seen : 0u;
+          chunk = min((uint32_t)FS2_WF_CHUNK, max(32u, (left / (2u * n_warps)) & ~31u));
+          b = atomicAdd(B.counters + 2, chunk);
+        }
         b = __shfl_sync(FULL, b, 0);
+        chunk = __shfl_sync(FULL, chunk, 0);
         if (b >= n_in) {
           exhausted = true;
         } else {
@@ -204,7 +223,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
       if (avail) {
         uint32_t rank = (uint32_t)__popc(idle & ((1u << lane) - 1u));
         if (w.st == PH_IDLE && rank < avail) {
-          idx = chunk_next + rank;
+          idx = wf_phys(chunk_next + rank, n_sec, B.cap);
           ray = wf_load_ray(st, B.cap, idx);
           q = ph_segment_start(S, w, ray);
         }
@@ -240,13 +259,14 @@ __global__ void __launch_bounds__(128)
 k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
            unsigned long long* __restrict__ stats) {
   const unsigned FULL = 0xFFFFFFFFu;
-  const uint32_t n_in = FRESH ? B.cap : B.counters[0];
+  const uint32_t n_sec = FRESH ? 0u : B.counters[0];
+  const uint32_t n_in = FRESH ? B.cap : n_sec + B.counters[8];
   if (blockIdx.x * 128u >= n_in) return;  // whole block past the live paths
   const uint32_t cur = B.counters[3] & 1u;
-  const uint32_t idx = blockIdx.x * 128u + threadIdx.x;
+  const uint32_t idx = wf_phys(blockIdx.x * 128u + threadIdx.x, n_sec, B.cap);
   const int lane = threadIdx.x & 31;
-  const bool have = idx < n_in;
-  bool alive = false, need = FRESH && have;
+  const bool have = blockIdx.x * 128u + threadIdx.x < n_in;
+  bool alive = false, need = FRESH && have, fresh = false;
   uint32_t n_shade = 0, finished = 0, pixslot = 0;
   PathState ps;
   ps.sum = v3(0.f, 0.f, 0.f);
@@ -274,7 +294,7 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
     const int leader = __ffs(m) - 1;
     unsigned long long base = 0;
     if (lane == leader)
-      base = atomicAdd((unsigned long long*)(B.counters + 4), (unsigned long long)__popc(m));
+      base = atomicAdd(B.next_path, (unsigned long long)__popc(m));
     base = __shfl_sync(FULL, base, leader);
     if (need) {
       unsigned long long id = base + (unsigned)__popc(m & ((1u << lane) - 1u));
@@ -287,22 +307,29 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
         wf_slot_pixel(B, pixslot, px, py);
         if (px < film.width && py < film.height) {  // else: padding pixel, take another id
           begin_path(cam, tp, (uint32_t)(py * film.width + px), px, py, ps);
-          alive = true;
+          alive = fresh = true;
           need = false;
         }
       }
     }
   }
-  // ---- compaction: live lanes write their state densely into the other array
-  unsigned ma = __ballot_sync(FULL, alive);
-  if (ma) {
-    const int leader = __ffs(ma) - 1;
-    uint32_t base = 0;
-    if (lane == leader) base = atomicAdd(B.counters + 1, (uint32_t)__popc(ma));
-    base = __shfl_sync(FULL, base, leader);
-    if (alive)
-      wf_store_path(B.state[cur ^ 1u], B.cap, base + (uint32_t)__popc(ma & ((1u << lane) - 1u)), ps,
-                    pixslot);
+  // ---- compaction: live lanes write their state densely into the other array, bounce paths
+  // from the front, new camera paths from the back
+  unsigned ms = __ballot_sync(FULL, alive && !fresh), mp = __ballot_sync(FULL, alive && fresh);
+  if (ms | mp) {
+    uint32_t bs = 0, bp = 0;
+    if (lane == 0) {
+      if (ms) bs = atomicAdd(B.counters + 1, (uint32_t)__popc(ms));
+      if (mp) bp = atomicAdd(B.counters + 7, (uint32_t)__popc(mp));
+    }
+    bs = __shfl_sync(FULL, bs, 0);
+    bp = __shfl_sync(FULL, bp, 0);
+    const unsigned below = (1u << lane) - 1u;
+    if (alive) {
+      uint32_t pos = fresh ? B.cap - 1u - (bp + (uint32_t)__popc(mp & below))
+                           : bs + (uint32_t)__popc(ms & below);
+      wf_store_path(B.state[cur ^ 1u], B.cap, pos, ps, pixslot);
+    }
   }
   if (!FRESH) {
     warp_add(stats + ST_PATHS, finished);
