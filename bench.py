@@ -237,11 +237,11 @@ def run_gpu(args, rank, world, local_rank):
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")  # > 126 MB L2
     first, n_mine, stride = multi_gpu.shard_samples(SPP, rank, world)
     KERNEL_NAME[0] = {"phase": "k_trace_phase<0> (leaf BVH, warp-synchronous phases)",
-                      "wavefront": "k_wf_trace<0> (wavefront: traversal only)",
+                      "wavefront": "k_wf_trace<0> + k_wf_shade<0> + k_wf_flip (all launches of one fs_trace)",
                       "lbvh_lane": "k_trace_mega<0,1> (leaf BVH, free-running lanes)",
                       "coop": "k_trace_coop<0> (linear leaves, warp-cooperative)",
                       "per_thread": "k_trace_mega<0,0> (linear leaves)"}[args.variant]
-    variant = {"phase": 0, "wavefront": abi.FS_TRACE_WAVEFRONT, "lbvh_lane": abi.FS_TRACE_LBVH_LANE, "coop": abi.FS_TRACE_COOP,
+    variant = {"phase": abi.FS_TRACE_MEGAKERNEL, "wavefront": abi.FS_TRACE_DEFAULT, "lbvh_lane": abi.FS_TRACE_LBVH_LANE, "coop": abi.FS_TRACE_COOP,
                "per_thread": abi.FS_TRACE_PER_THREAD}[args.variant]
     flags = abi.FS_TRACE_NO_RESOLVE | abi.FS_TRACE_ASYNC | variant
 
@@ -368,7 +368,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="fs2")
     ap.add_argument("--skip-cpu", action="store_true", help="tuning runs: no cpu_baseline leg")
-    ap.add_argument("--variant", default="phase", choices=["phase", "wavefront", "lbvh_lane", "coop", "per_thread"],
+    ap.add_argument("--variant", default="wavefront", choices=["phase", "wavefront", "lbvh_lane", "coop", "per_thread"],
                     help="leaf-scan variant of the trace kernel (A/B measurements)")
     args = ap.parse_args()
     rank = int(os.environ.get("RANK", "0"))

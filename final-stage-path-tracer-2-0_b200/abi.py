@@ -23,6 +23,7 @@ FS_TRACE_ASYNC = 16
 FS_TRACE_PER_THREAD = 32
 FS_TRACE_COOP = 64
 FS_TRACE_LBVH_LANE = 128
+FS_TRACE_MEGAKERNEL = 256
 
 # numpy dtypes of the flattened arrays -------------------------------------------------
 NODE_DT = np.dtype([("bmin", "<f4", 3), ("first", "<u4"), ("bmax", "<f4", 3), ("count", "<u4")])

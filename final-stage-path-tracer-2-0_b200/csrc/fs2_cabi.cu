@@ -617,7 +617,8 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
     const bool coop = (flags & FS_TRACE_COOP) != 0;
     const bool st = ctx->stats_build;
 #define FS2_LAUNCH(K) K<<<grid, 128, 0, ctx->stream>>>(ctx->ds, cb, film, tp, ctx->d_stats)
-    if (flags & FS_TRACE_WAVEFRONT) {
+    const int mega = FS_TRACE_PER_THREAD | FS_TRACE_COOP | FS_TRACE_LBVH_LANE | FS_TRACE_MEGAKERNEL;
+    if (!(flags & mega)) {
       if ((rc = launch_wavefront(ctx, cb, film, tp))) return rc;
       ctx->launches--;  // the common increment below counts one launch
     } else if (per_thread) {

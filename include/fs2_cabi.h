@@ -188,17 +188,21 @@ typedef struct fs_camera {
 } fs_camera;
 
 /* fs_trace flags */
-#define FS_TRACE_DEFAULT 0
+#define FS_TRACE_DEFAULT 0     /* wavefront pipeline: path pool in HBM, traversal and shading kernels */
 #define FS_TRACE_NO_JITTER 1  /* pixel-centre rays (TraceRange ray construction) */
 #define FS_TRACE_NO_DOF 2     /* ignore aperture_size                            */
-#define FS_TRACE_WAVEFRONT 4  /* use the wavefront pipeline instead of the megakernel */
+#define FS_TRACE_WAVEFRONT 4  /* the default, named (kept for callers that set it) */
 #define FS_TRACE_NO_RESOLVE 8 /* skip the mean/gamma resolve (multi-GPU: resolve after the reduce) */
-#define FS_TRACE_ASYNC 16     /* enqueue only: no stream synchronisation before returning */
-#define FS_TRACE_PER_THREAD 32 /* every thread scans its own mesh leaves linearly, in reference order */
-#define FS_TRACE_COOP 64       /* linear leaf scans done by the whole warp, 32 triangles per step */
-#define FS_TRACE_LBVH_LANE 128 /* per-leaf 4-wide BVH walked by free-running lanes (nested loops) */
-/* default (none of the three): the per-leaf 4-wide BVH built by fs_scene_upload, walked by a
- * warp-synchronous phase machine (all lanes in the same traversal state step together) */
+#define FS_TRACE_ASYNC 16     /* do not wait for the result: the film is complete in stream order */
+#define FS_TRACE_PER_THREAD 32 /* megakernel; every thread scans its own mesh leaves linearly, in reference order */
+#define FS_TRACE_COOP 64       /* megakernel; linear leaf scans done by the whole warp, 32 triangles per step */
+#define FS_TRACE_LBVH_LANE 128 /* megakernel; per-leaf 4-wide BVH walked by free-running lanes (nested loops) */
+#define FS_TRACE_MEGAKERNEL 256 /* megakernel; warp-synchronous phase machine over the leaf BVH (one launch,
+                                 * a pixel's samples are summed in order: bit-reproducible films) */
+/* default (none of the four megakernel flags): the wavefront pipeline.  Its traversal kernel is
+ * the same phase machine over the per-leaf 4-wide BVH built by fs_scene_upload; every path has
+ * the RNG stream and arithmetic of the megakernels, but a pixel's samples reach the film through
+ * float atomics, so films agree with the megakernels to summation order, not bit for bit. */
 
 typedef struct fs_stats {
   uint64_t n_paths;    /* camera paths traced since the last reset           */

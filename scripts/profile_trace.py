@@ -15,12 +15,12 @@ import fs2_b200  # noqa: E402
 import gen_scenes  # noqa: E402
 from fs2_b200 import abi, host  # noqa: E402
 
-variant = sys.argv[1] if len(sys.argv) > 1 else "phase"
+variant = sys.argv[1] if len(sys.argv) > 1 else "wavefront"
 spp = int(sys.argv[2]) if len(sys.argv) > 2 else 8
 width = int(sys.argv[3]) if len(sys.argv) > 3 else 1920
 height = int(sys.argv[4]) if len(sys.argv) > 4 else 1080
 scene = sys.argv[5] if len(sys.argv) > 5 else "mesh100k"
-flags = {"phase": 0, "wavefront": abi.FS_TRACE_WAVEFRONT, "lbvh_lane": abi.FS_TRACE_LBVH_LANE,
+flags = {"phase": abi.FS_TRACE_MEGAKERNEL, "wavefront": abi.FS_TRACE_DEFAULT, "lbvh_lane": abi.FS_TRACE_LBVH_LANE,
          "coop": abi.FS_TRACE_COOP, "per_thread": abi.FS_TRACE_PER_THREAD}[variant]
 cache = os.path.join(REPO, "scenes", "_cache")
 path = gen_scenes.generate(cache, [scene])[scene]

@@ -107,7 +107,7 @@ def _variants_agree(ctx, scene, cam, w, h, spp):
     ctx.upload(scene)
     ctx.resize(w, h)
     out = []
-    for flags in (0, fs2_b200.FS_TRACE_LBVH_LANE, fs2_b200.FS_TRACE_WAVEFRONT,
+    for flags in (fs2_b200.FS_TRACE_MEGAKERNEL, fs2_b200.FS_TRACE_LBVH_LANE, fs2_b200.FS_TRACE_DEFAULT,
                   fs2_b200.FS_TRACE_COOP, fs2_b200.FS_TRACE_PER_THREAD):
         ctx.reset()
         ctx.reset_stats()
