@@ -313,14 +313,15 @@ k_trace_coop(DScene S, CamBasis cam, Film film, TraceParams tp,
 
 // Variant C (default) — warp-synchronous phase machine (fs2_phase.cuh) over the leaf BVH.
 // Same per-pixel ownership and path regeneration as the other variants.
-#define FS2_PHASE(STATE, MAXREP, CALL)                                   \
+#define FS2_PHASE_N(STATE, MAXREP, MINLANES, CALL)                       \
   _Pragma("unroll 1") for (int rep_ = 0; rep_ < (MAXREP); ++rep_) {      \
     unsigned m_ = __ballot_sync(0xFFFFFFFFu, w.st == (STATE));           \
-    if (!m_ || (rep_ && __popc(m_) < FS2_PH_REPEAT_MIN)) break;          \
+    if (!m_ || (rep_ && __popc(m_) < (MINLANES))) break;                 \
     if (w.st == (STATE)) {                                               \
       CALL;                                                              \
     }                                                                    \
   }
+#define FS2_PHASE(STATE, MAXREP, CALL) FS2_PHASE_N(STATE, MAXREP, FS2_PH_REPEAT_MIN, CALL)
 
 template <bool STATS>
 __global__ void __launch_bounds__(FS2_PH_THREADS, 4)

@@ -42,6 +42,9 @@ namespace fs2 {
 // counters (uint32): 0 continuing paths of this wave, 1 continuing paths of the next wave,
 //                    2 fetch cursor of k_wf_trace, 3 current state array, 6 waves run,
 //                    7 new camera paths of the next wave, 8 new camera paths of this wave
+// (Tried and dropped: tracing the bounce rays in direction-octant order through per-octant index
+// lists changed nothing, 383.5 vs 386.3 Mpaths/s: lanes diverge by traversal stage, not by the
+// order in which they visit octree children.)
 // A wave's array holds the continuing (bounce) paths from the front and the camera paths
 // started by the last shade kernel from the back, so warps of k_wf_trace pull either
 // coherent camera rays or bounce rays, not a mix of both.
@@ -163,6 +166,28 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
   __threadfence_system();
 }
 
+// most consecutive executions of a phase per loop iteration; a repeat needs FS2_WF_REPEAT_MIN
+// lanes still in the phase.  Measured on config 2 (Mpaths/s): min 12 / reps 3,2,2,2,4 -> 352;
+// min 20 -> 342; no repeats -> 369; min 6 -> 382; min 6 / reps 3,3,3,3,4 -> 386; min 4 -> 376;
+// min 3 -> 368; min 1 -> 359.
+#ifndef FS2_WF_REPEAT_MIN
+#define FS2_WF_REPEAT_MIN 6
+#endif
+#ifndef FS2_WF_REP_OBJ
+#define FS2_WF_REP_OBJ 3
+#endif
+#ifndef FS2_WF_REP_ENTER
+#define FS2_WF_REP_ENTER 3
+#endif
+#ifndef FS2_WF_REP_NODE
+#define FS2_WF_REP_NODE 3
+#endif
+#ifndef FS2_WF_REP_TRIS
+#define FS2_WF_REP_TRIS 3
+#endif
+#ifndef FS2_WF_REP_RETURN
+#define FS2_WF_REP_RETURN 4
+#endif
 #ifndef FS2_WF_MIN_BLOCKS
 #define FS2_WF_MIN_BLOCKS 5  // measured: 4 -> 262, 5 -> 294, 6 -> 287 (64 B of spills), 8 -> 268 Mpaths/s
 #endif
@@ -178,6 +203,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   const uint32_t n_in = n_sec + B.counters[8];
   const float4* st = B.state[B.counters[3] & 1u];
   const uint32_t n_warps = gridDim.x * (FS2_PH_THREADS / 32);
+
   Counters c = {0, 0, 0, 0, 0, 0};
   Ray ray = make_ray(v3(0.f, 0.f, 0.f), v3(0.f, 0.f, 0.f));
   LbRay q = make_lbray(ray);
@@ -232,11 +258,11 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
         break;
       }
     }
-    FS2_PHASE(PH_OBJ, 3, ph_object<STATS>(S, w, ray, c))
-    FS2_PHASE(PH_ENTER, 2, ph_enter<STATS>(S, w, ray, sm, c))
-    FS2_PHASE(PH_LB_NODE, 2, ph_lb_node<STATS>(S, w, ray, q, sm, c))
-    FS2_PHASE(PH_LB_TRIS, 2, ph_lb_tris<STATS>(S, w, ray, sm, c))
-    FS2_PHASE(PH_RETURN, 4, ph_return(S, w, ray, sm))
+    FS2_PHASE_N(PH_OBJ, FS2_WF_REP_OBJ, FS2_WF_REPEAT_MIN, ph_object<STATS>(S, w, ray, c))
+    FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, ph_enter<STATS>(S, w, ray, sm, c))
+    FS2_PHASE_N(PH_LB_NODE, FS2_WF_REP_NODE, FS2_WF_REPEAT_MIN, ph_lb_node<STATS>(S, w, ray, q, sm, c))
+    FS2_PHASE_N(PH_LB_TRIS, FS2_WF_REP_TRIS, FS2_WF_REPEAT_MIN, ph_lb_tris<STATS>(S, w, ray, sm, c))
+    FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, ph_return(S, w, ray, sm))
     if (w.st == PH_SHADE) {  // nearest hit of the segment is final
       wf_store_hit(B, idx, w.rec);
       w.st = PH_IDLE;
@@ -325,9 +351,10 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
     bs = __shfl_sync(FULL, bs, 0);
     bp = __shfl_sync(FULL, bp, 0);
     const unsigned below = (1u << lane) - 1u;
+    uint32_t pos = 0;
     if (alive) {
-      uint32_t pos = fresh ? B.cap - 1u - (bp + (uint32_t)__popc(mp & below))
-                           : bs + (uint32_t)__popc(ms & below);
+      pos = fresh ? B.cap - 1u - (bp + (uint32_t)__popc(mp & below))
+                  : bs + (uint32_t)__popc(ms & below);
       wf_store_path(B.state[cur ^ 1u], B.cap, pos, ps, pixslot);
     }
   }
