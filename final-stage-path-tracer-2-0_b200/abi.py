@@ -67,6 +67,11 @@ class fs_camera(C.Structure):
                 ("z_far", C.c_float), ("fast_render_enabled", C.c_int32)]
 
 
+class fs_mesh_tree(C.Structure):
+    _fields_ = [("nodes", C.c_void_p), ("tri_plane", C.c_void_p), ("tri_aux", C.c_void_p),
+                ("n_nodes", C.c_uint32), ("n_tris", C.c_uint32), ("build_ms", C.c_float)]
+
+
 class fs_stats(C.Structure):
     _fields_ = [("n_paths", C.c_uint64), ("n_segments", C.c_uint64), ("n_node", C.c_uint64),
                 ("n_tri", C.c_uint64), ("n_bary", C.c_uint64), ("n_prim", C.c_uint64),

@@ -16,7 +16,10 @@
 #include <string>
 #include <vector>
 
+#include <cub/device/device_scan.cuh>
+
 #include "fs2_kernels.cuh"
+#include "fs2_build.cuh"
 #include "fs2_lbvh_build.h"
 
 using namespace fs2;
@@ -339,6 +342,8 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   CUDA_TRY(ctx, cudaGetLastError());
   return FS_OK;
 }
+
+#include "fs2_build_host.inc"
 
 }  // namespace
 
@@ -744,6 +749,31 @@ int fs_get_stream(fs_ctx* ctx, void** stream) {
   if (!ctx || !stream) return fail(ctx, FS_E_INVALID, "null argument");
   *stream = (void*)ctx->stream;
   return FS_OK;
+}
+
+int fs_mesh_tree_build(int device, const float* verts, uint32_t n_verts, const uint32_t* face_vertices,
+                       const float* face_planes, uint32_t n_faces, uint32_t face_base,
+                       uint32_t node_base, uint32_t tri_base, fs_mesh_tree* out) {
+  if (!out) return fail(nullptr, FS_E_INVALID, "fs_mesh_tree_build: null out");
+  memset(out, 0, sizeof *out);
+  if (!verts || !face_vertices || !face_planes || !n_verts || !n_faces)
+    return fail(nullptr, FS_E_INVALID, "fs_mesh_tree_build: empty mesh");
+  for (size_t i = 0; i < 3 * (size_t)n_faces; i++)
+    if (face_vertices[i] >= n_verts)
+      return fail(nullptr, FS_E_INVALID, "fs_mesh_tree_build: vertex index out of range");
+  cudaError_t e = cudaSetDevice(device);
+  if (e != cudaSuccess) return fail(nullptr, FS_E_CUDA, "cudaSetDevice(%d): %s", device, cudaGetErrorString(e));
+  int rc = bd_build(verts, n_verts, face_vertices, face_planes, n_faces, face_base, node_base, tri_base, out);
+  if (rc != FS_OK) fs_mesh_tree_free(out);
+  return rc;
+}
+
+void fs_mesh_tree_free(fs_mesh_tree* t) {
+  if (!t) return;
+  free(t->nodes);
+  free(t->tri_plane);
+  free(t->tri_aux);
+  memset(t, 0, sizeof *t);
 }
 
 }  // extern "C"

@@ -9,6 +9,10 @@ from . import abi, build
 
 _SYMBOLS = {
     "fs_abi_version": (C.c_int, []),
+    "fs_mesh_tree_build": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
+                                     C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
+                                     C.POINTER(abi.fs_mesh_tree)]),
+    "fs_mesh_tree_free": (None, [C.POINTER(abi.fs_mesh_tree)]),
     "fs_last_error": (C.c_char_p, [C.c_void_p]),
     "fs_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int]),
     "fs_destroy": (C.c_int, [C.c_void_p]),

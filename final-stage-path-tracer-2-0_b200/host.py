@@ -42,6 +42,8 @@ def load_host_library():
                                      C.c_float, C.c_float]
     lib.fs2h_set_device.argtypes = [C.c_int]
     lib.fs2h_set_seed.argtypes = [C.c_uint64]
+    lib.fs2h_set_gpu_build.argtypes = [C.c_int]
+    lib.fs2h_gpu_build_ms.restype = C.c_float
     lib.fs2h_last_error.restype = C.c_char_p
     _lib = lib
     return lib

@@ -5,6 +5,7 @@
 #include <stdio.h>
 
 #include "fs2_impl.h"
+#include "fs2_octree.h"
 
 namespace {
 
@@ -218,6 +219,9 @@ float fs2h_trace_range(void* scene, const fs_camera* cam, void* frame, float x, 
 }
 void fs2h_set_device(int device) { base::SetTraceDevice(device); }
 void fs2h_set_seed(uint64_t seed) { base::SetTraceSeed(seed); }
+// Mesh octrees are built by the CUDA library on `device` (-1: by the host builder).
+void fs2h_set_gpu_build(int device) { fs2h::gpu_build_device() = device; }
+float fs2h_gpu_build_ms() { return fs2h::gpu_build_ms(); }
 const char* fs2h_last_error() { return base::LastTraceError(); }
 
 }  // extern "C"

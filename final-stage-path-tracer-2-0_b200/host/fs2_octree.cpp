@@ -12,11 +12,27 @@
 // references are appended in that same depth-first order.
 #include "fs2_octree.h"
 
+#include <stdio.h>
+#include <stdlib.h>
+
 #include <algorithm>
 #include <atomic>
 #include <thread>
 
 namespace fs2h {
+
+// GPU build switch: fs2h_set_gpu_build(device) / env FS2_GPU_BUILD=<device>; -1 = host build.
+int& gpu_build_device() {
+  static int dev = [] {
+    const char* e = getenv("FS2_GPU_BUILD");
+    return e && *e ? atoi(e) : -1;
+  }();
+  return dev;
+}
+float& gpu_build_ms() {
+  static float ms = 0.f;
+  return ms;
+}
 
 namespace {
 
@@ -200,6 +216,36 @@ uint32_t build_mesh_tree(const std::vector<Vec3>& verts, std::vector<MeshFaceRec
     all[i] = i;
   }
   uint32_t root_index = (uint32_t)out->nodes.size();
+  if (gpu_build_device() >= 0) {
+    // same tree, built by the CUDA library (csrc/fs2_build.cuh); byte-identical output
+    std::vector<float> vbuf(3 * verts.size()), pbuf(4 * faces.size());
+    std::vector<uint32_t> ibuf(3 * faces.size());
+    for (size_t i = 0; i < verts.size(); i++) {
+      vbuf[3 * i] = verts[i].x;
+      vbuf[3 * i + 1] = verts[i].y;
+      vbuf[3 * i + 2] = verts[i].z;
+    }
+    for (size_t i = 0; i < faces.size(); i++) {
+      for (int k = 0; k < 3; k++) ibuf[3 * i + k] = faces[i].v[k];
+      pbuf[4 * i] = faces[i].plane.x;
+      pbuf[4 * i + 1] = faces[i].plane.y;
+      pbuf[4 * i + 2] = faces[i].plane.z;
+      pbuf[4 * i + 3] = faces[i].plane.w;
+    }
+    fs_mesh_tree t;
+    int rc = fs_mesh_tree_build(gpu_build_device(), vbuf.data(), (uint32_t)verts.size(), ibuf.data(),
+                                pbuf.data(), (uint32_t)faces.size(), face_base, root_index,
+                                (uint32_t)out->tri_aux.size(), &t);
+    if (rc == FS_OK) {
+      out->nodes.insert(out->nodes.end(), t.nodes, t.nodes + t.n_nodes);
+      out->tri_plane.insert(out->tri_plane.end(), t.tri_plane, t.tri_plane + 4 * (size_t)t.n_tris);
+      out->tri_aux.insert(out->tri_aux.end(), t.tri_aux, t.tri_aux + t.n_tris);
+      gpu_build_ms() += t.build_ms;
+      fs_mesh_tree_free(&t);
+      return root_index;
+    }
+    fprintf(stderr, "fs2: GPU octree build failed (%s); building on the host\n", fs_last_error(nullptr));
+  }
   out->nodes.resize(root_index + 1);
   MeshBuild mb{&verts, &faces, face_base, out, threads ? threads : 1};
   build_mesh_node(mb, root_index, root, 0, all);

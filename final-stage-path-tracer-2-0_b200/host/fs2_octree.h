@@ -32,6 +32,10 @@ struct FlatArrays {
   uint32_t sky = 0;
 };
 
+// Device the mesh octrees are built on (-1: on the host), and the device time spent there.
+int& gpu_build_device();
+float& gpu_build_ms();
+
 bool triangle_touches_box(Vec3 p1, Vec3 p2, Vec3 p3, const Box& b);
 bool box_touches_box(const Box& a, const Box& b);
 void child_boxes(const Box& parent, Box out[8]);

@@ -283,6 +283,32 @@ int fs_reset_stats(fs_ctx* ctx);
 int fs_get_stream(fs_ctx* ctx, void** stream);
 int fs_set_stream(fs_ctx* ctx, void* stream);
 
+/*
+ * GPU build of one mesh octree: replaces MeshBvh::BuildBvh / MeshBvhNode::Subdivide
+ * (reference source/mesh.cpp:39-76,117-152; SAT test source/math/intersect.cpp:193-311) and
+ * the packing of the leaf records.  Same leaf membership, leaf order, node numbering and
+ * record bytes as the host builder (host/fs2_octree.cpp build_mesh_tree).
+ *   verts          3 floats per vertex
+ *   face_vertices  3 vertex indices per face
+ *   face_planes    4 floats per face (MeshFace::plane, never all zero)
+ *   face_base      global index of this mesh's face 0 (fs_tri_aux::face)
+ *   node_base      index the returned nodes[0] will have in fs_scene_desc::nodes
+ *   tri_base       index the returned record 0 will have in tri_plane / tri_aux
+ * The arrays of `out` are malloc'ed; release them with fs_mesh_tree_free.
+ */
+typedef struct fs_mesh_tree {
+  fs_node* nodes;
+  float* tri_plane;
+  fs_tri_aux* tri_aux;
+  uint32_t n_nodes, n_tris;
+  float build_ms; /* device time from the first to the last build kernel (CUDA events) */
+} fs_mesh_tree;
+
+int fs_mesh_tree_build(int device, const float* verts, uint32_t n_verts, const uint32_t* face_vertices,
+                       const float* face_planes, uint32_t n_faces, uint32_t face_base,
+                       uint32_t node_base, uint32_t tri_base, fs_mesh_tree* out);
+void fs_mesh_tree_free(fs_mesh_tree* tree);
+
 #ifdef __cplusplus
 }
 #endif

@@ -15,15 +15,22 @@
 #include <math.h>
 #include "fs2_cabi.h"
 
+/* Function qualifier: a CUDA translation unit defines it as
+ * `static inline __host__ __device__` so the GPU octree builder packs records with this
+ * very source (csrc/fs2_build.cuh). */
+#ifndef FS2_PACK_FN
+#define FS2_PACK_FN static inline
+#endif
+
 /* Axis dropped by triangle_planar_map_vectors (intersect.cpp:118-128):
  * 0 = x (map to yz), 1 = y (map to xz), 2 = z (map to xy). */
-static inline int fs_pack_drop_axis(const float plane[4]) {
+FS2_PACK_FN int fs_pack_drop_axis(const float plane[4]) {
   float ax = fabsf(plane[0]), ay = fabsf(plane[1]), az = fabsf(plane[2]);
   if (ax >= ay) return (ax >= az) ? 0 : 2;
   return (ay >= az) ? 1 : 2;
 }
 
-static inline void fs_pack_triangle(const float p1[3], const float p2[3], const float p3[3],
+FS2_PACK_FN void fs_pack_triangle(const float p1[3], const float p2[3], const float p3[3],
                                     const float plane[4], uint32_t face_index,
                                     float out_plane[4], fs_tri_aux* aux) {
   float v0[3], v1[3];

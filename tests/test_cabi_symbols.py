@@ -14,7 +14,7 @@ REPO = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
 def header_functions():
     text = open(os.path.join(REPO, "include", "fs2_cabi.h")).read()
     text = re.sub(r"/\*.*?\*/", "", text, flags=re.S)
-    return sorted(set(re.findall(r"^\s*(?:int|const char\s*\*)\s*(fs_[a-z_]+)\s*\(", text, re.M)))
+    return sorted(set(re.findall(r"^\s*(?:int|void|const char\s*\*)\s*(fs_[a-z_]+)\s*\(", text, re.M)))
 
 
 def test_every_declared_symbol_is_exported():
