@@ -303,10 +303,10 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   const unsigned long long max_waves = 8ull * ((total + pool - 1) / pool) + 8ull;
   const unsigned smem = ph_smem_bytes(ctx->ds.scene_root >= 0);
   int per_sm = 0;
-  if (ctx->stats_build)
-    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_trace<true>, FS2_PH_THREADS, smem));
-  else
-    CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_wf_trace<false>, FS2_PH_THREADS, smem));
+  void (*trace_kernel)(DScene, WfBuffers, TraceParams, unsigned long long*) =
+      ctx->stats_build ? (ctx->ds.scene_root >= 0 ? k_wf_trace<true, true> : k_wf_trace<true, false>)
+                       : (ctx->ds.scene_root >= 0 ? k_wf_trace<false, true> : k_wf_trace<false, false>);
+  CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_kernel, FS2_PH_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   const int persistent = ctx->sm_count * per_sm;  // one resident generation of CTAs
   const uint32_t shade_blocks = cap / 128u;
@@ -326,10 +326,7 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
       running++;
       k_wf_flip<<<1, 1, 0, streams[p]>>>(B[p].counters, B[p].host_live);
       CUDA_TRY(ctx, cudaEventRecord(ev, streams[p]));
-      if (ctx->stats_build)
-        k_wf_trace<true><<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
-      else
-        k_wf_trace<false><<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
+      trace_kernel<<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
       k_wf_shade<false><<<shade_blocks, 128, 0, streams[p]>>>(ctx->ds, cb, film, tp, B[p], ctx->d_stats);
       ctx->launches += 3;
     }
@@ -382,10 +379,16 @@ int fs_create(fs_ctx** out, int device, int flags) {
       e1 = cudaFuncSetAttribute(k_trace_phase<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 FS2_PH_SMEM_BYTES);
     if (e1 == cudaSuccess)
-      e1 = cudaFuncSetAttribute(k_wf_trace<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      e1 = cudaFuncSetAttribute(k_wf_trace<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 FS2_PH_SMEM_BYTES);
     if (e1 == cudaSuccess)
-      e1 = cudaFuncSetAttribute(k_wf_trace<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+      e1 = cudaFuncSetAttribute(k_wf_trace<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                FS2_PH_SMEM_BYTES);
+    if (e1 == cudaSuccess)
+      e1 = cudaFuncSetAttribute(k_wf_trace<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                FS2_PH_SMEM_BYTES);
+    if (e1 == cudaSuccess)
+      e1 = cudaFuncSetAttribute(k_wf_trace<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                 FS2_PH_SMEM_BYTES);
     if (e1 == cudaSuccess)
       e1 = cudaDeviceGetAttribute(&ctx->sm_count, cudaDevAttrMultiProcessorCount, device);

@@ -98,11 +98,14 @@ struct PhSmem {
 // frame words: 0 node, 1 bits, 2..4 tx ty tz, 5..7 sx sy sz   (struct Frame, fs2_traverse.cuh)
 
 // Begin Scene::Trace for the lane's next ray (scene.cpp:227-237).
+// (TREE = false in the ph_* steps: the caller knows the scene has no scene octree, so the
+// scene-leaf bookkeeping folds away at compile time.)
+template <bool TREE = true>
 __device__ __forceinline__ LbRay ph_segment_start(const DScene& S, PhLane& w, const Ray& r) {
   w.rec = no_hit();
   w.flags = 0;
   w.ssp = 0;
-  if (S.scene_root < 0) {
+  if (!TREE || S.scene_root < 0) {
     w.obj_i = 0;
     w.st = PH_OBJ;
   } else {
@@ -115,10 +118,10 @@ __device__ __forceinline__ LbRay ph_segment_start(const DScene& S, PhLane& w, co
 // ------------------------------------------------------------------ octree steps
 // "call" node w.cur of the active tree (reference mesh.cpp:78-84 / scene.cpp:76-83, then
 // bvh.h:160-186).  Same arithmetic as walk_octree().
-template <bool STATS>
+template <bool STATS, bool TREE = true>
 __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& r,
                                          const PhSmem& sm, Counters& c) {
-  const bool mesh = (w.flags & PH_F_MESH) != 0;
+  const bool mesh = !TREE || (w.flags & PH_F_MESH) != 0;  // without a scene tree only meshes walk
   NodeRec n = load_node(S, w.cur);
   float nparam;
   V3 entry = r.start;
@@ -202,9 +205,10 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
 
 // Return (w.flags & PH_F_RET) into the enclosing frame of the active tree (bvh.h:189-228),
 // or finish the tree when no frame is left.  One frame per call.
+template <bool TREE = true>
 __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray& r,
                                           const PhSmem& sm) {
-  const bool mesh = (w.flags & PH_F_MESH) != 0;
+  const bool mesh = !TREE || (w.flags & PH_F_MESH) != 0;
   int& sp = mesh ? w.msp : w.ssp;
   bool ret = (w.flags & PH_F_RET) != 0;
   if (sp == 0) {
@@ -214,7 +218,7 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
     }
     // MeshObject::Trace finished with `ret` (mesh.cpp:277-322)
     w.flags &= ~PH_F_MESH;
-    if (S.scene_root >= 0 && ret && w.rec.param < w.glob.param) {
+    if (TREE && S.scene_root >= 0 && ret && w.rec.param < w.glob.param) {
       w.glob = w.rec;
       w.flags |= PH_F_SIMPROVED;
     }
@@ -274,10 +278,10 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
 // ------------------------------------------------------------------ object iteration
 // One object of the brute-force list (scene.cpp:230-233) or of the current scene-tree leaf
 // (scene.cpp:84-99).  Primitives are tested on the spot, a mesh starts its octree walk.
-template <bool STATS>
+template <bool STATS, bool TREE = true>
 __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray& r, Counters& c) {
   uint32_t oi;
-  const bool tree = S.scene_root >= 0;
+  const bool tree = TREE && S.scene_root >= 0;
   if (!tree) {
     if (w.obj_i >= S.n_objects) {
       w.st = PH_SHADE;

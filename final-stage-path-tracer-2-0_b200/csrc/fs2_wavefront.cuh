@@ -189,9 +189,11 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #define FS2_WF_REP_RETURN 4
 #endif
 #ifndef FS2_WF_MIN_BLOCKS
-#define FS2_WF_MIN_BLOCKS 5  // measured: 4 -> 262, 5 -> 294, 6 -> 287 (64 B of spills), 8 -> 268 Mpaths/s
+#define FS2_WF_MIN_BLOCKS 6  // measured (no scene tree, Mpaths/s): 5 -> 400 (92 regs), 6 -> 433 (80 regs, 12 B spilled), 7 -> 434, 8 -> 398
 #endif
-template <bool STATS>
+// TREE = false: the scene has no scene octree (< 182 objects), which lets the
+// compiler drop the scene-leaf bookkeeping (second hit record, leaf cursor) from the loop.
+template <bool STATS, bool TREE>
 __global__ void __launch_bounds__(FS2_PH_THREADS, FS2_WF_MIN_BLOCKS)
 k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict__ stats) {
   extern __shared__ uint32_t ph_smem[];
@@ -251,18 +253,18 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
         if (w.st == PH_IDLE && rank < avail) {
           idx = wf_phys(chunk_next + rank, n_sec, B.cap);
           ray = wf_load_ray(st, B.cap, idx);
-          q = ph_segment_start(S, w, ray);
+          q = ph_segment_start<TREE>(S, w, ray);
         }
         chunk_next += min((uint32_t)__popc(idle), avail);
       } else if (exhausted && idle == FULL) {
         break;
       }
     }
-    FS2_PHASE_N(PH_OBJ, FS2_WF_REP_OBJ, FS2_WF_REPEAT_MIN, ph_object<STATS>(S, w, ray, c))
-    FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, ph_enter<STATS>(S, w, ray, sm, c))
+    FS2_PHASE_N(PH_OBJ, FS2_WF_REP_OBJ, FS2_WF_REPEAT_MIN, (ph_object<STATS, TREE>(S, w, ray, c)))
+    FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, (ph_enter<STATS, TREE>(S, w, ray, sm, c)))
     FS2_PHASE_N(PH_LB_NODE, FS2_WF_REP_NODE, FS2_WF_REPEAT_MIN, ph_lb_node<STATS>(S, w, ray, q, sm, c))
     FS2_PHASE_N(PH_LB_TRIS, FS2_WF_REP_TRIS, FS2_WF_REPEAT_MIN, ph_lb_tris<STATS>(S, w, ray, sm, c))
-    FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, ph_return(S, w, ray, sm))
+    FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, ph_return<TREE>(S, w, ray, sm))
     if (w.st == PH_SHADE) {  // nearest hit of the segment is final
       wf_store_hit(B, idx, w.rec);
       w.st = PH_IDLE;
