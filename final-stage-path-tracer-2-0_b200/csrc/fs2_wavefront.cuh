@@ -315,17 +315,27 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
       alive = true;
     }
   }
-  // ---- regeneration: the lanes that need a path take consecutive ids (one atomic per warp)
+  // Counter traffic is aggregated per CTA: with one atomic per warp on three shared addresses
+  // the kernel was bound by same-address atomic latency (ncu r1_h: 82 % long-scoreboard stalls
+  // on the atomics and the shuffles that wait for them).
+  __shared__ uint32_t s_cnt[4][2];
+  __shared__ unsigned long long s_base64;
+  __shared__ uint32_t s_base[2];
+  const int warp = threadIdx.x >> 5;
+  const unsigned below = (1u << lane) - 1u;
+  // ---- regeneration: the threads that need a path take consecutive ids
   for (;;) {
     unsigned m = __ballot_sync(FULL, need);
-    if (!m) break;
-    const int leader = __ffs(m) - 1;
-    unsigned long long base = 0;
-    if (lane == leader)
-      base = atomicAdd(B.next_path, (unsigned long long)__popc(m));
-    base = __shfl_sync(FULL, base, leader);
+    if (lane == 0) s_cnt[warp][0] = (uint32_t)__popc(m);
+    __syncthreads();
+    const uint32_t c0 = s_cnt[0][0], c1 = s_cnt[1][0], c2 = s_cnt[2][0], c3 = s_cnt[3][0];
+    const uint32_t tot = c0 + c1 + c2 + c3;
+    if (!tot) break;  // CTA-uniform
+    if (threadIdx.x == 0) s_base64 = atomicAdd(B.next_path, (unsigned long long)tot);
+    __syncthreads();
     if (need) {
-      unsigned long long id = base + (unsigned)__popc(m & ((1u << lane) - 1u));
+      uint32_t before = (warp > 0 ? c0 : 0u) + (warp > 1 ? c1 : 0u) + (warp > 2 ? c2 : 0u);
+      unsigned long long id = s_base64 + before + (unsigned)__popc(m & below);
       if (id >= B.total) {
         need = false;  // no camera paths left
       } else {
@@ -340,30 +350,46 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
         }
       }
     }
+    __syncthreads();  // s_cnt / s_base64 are rewritten by the next round
   }
-  // ---- compaction: live lanes write their state densely into the other array, bounce paths
-  // from the front, new camera paths from the back
+  // ---- compaction: live threads write their state densely into the other array, bounce
+  // paths from the front, new camera paths from the back
   unsigned ms = __ballot_sync(FULL, alive && !fresh), mp = __ballot_sync(FULL, alive && fresh);
-  if (ms | mp) {
-    uint32_t bs = 0, bp = 0;
-    if (lane == 0) {
-      if (ms) bs = atomicAdd(B.counters + 1, (uint32_t)__popc(ms));
-      if (mp) bp = atomicAdd(B.counters + 7, (uint32_t)__popc(mp));
-    }
-    bs = __shfl_sync(FULL, bs, 0);
-    bp = __shfl_sync(FULL, bp, 0);
-    const unsigned below = (1u << lane) - 1u;
-    uint32_t pos = 0;
-    if (alive) {
-      pos = fresh ? B.cap - 1u - (bp + (uint32_t)__popc(mp & below))
-                  : bs + (uint32_t)__popc(ms & below);
-      wf_store_path(B.state[cur ^ 1u], B.cap, pos, ps, pixslot);
-    }
+  __syncthreads();
+  if (lane == 0) {
+    s_cnt[warp][0] = (uint32_t)__popc(ms);
+    s_cnt[warp][1] = (uint32_t)__popc(mp);
+  }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    uint32_t t = s_cnt[0][threadIdx.x] + s_cnt[1][threadIdx.x] + s_cnt[2][threadIdx.x] + s_cnt[3][threadIdx.x];
+    s_base[threadIdx.x] = t ? atomicAdd(B.counters + (threadIdx.x ? 7 : 1), t) : 0u;
+  }
+  __syncthreads();
+  if (alive) {
+    const int k = fresh ? 1 : 0;
+    uint32_t off = s_base[k] + (warp > 0 ? s_cnt[0][k] : 0u) + (warp > 1 ? s_cnt[1][k] : 0u) +
+                   (warp > 2 ? s_cnt[2][k] : 0u) + (uint32_t)__popc((fresh ? mp : ms) & below);
+    wf_store_path(B.state[cur ^ 1u], B.cap, fresh ? B.cap - 1u - off : off, ps, pixslot);
   }
   if (!FRESH) {
-    warp_add(stats + ST_PATHS, finished);
-    warp_add(stats + ST_SEGMENTS, have ? 1u : 0u);
-    warp_add(stats + ST_SHADE, n_shade);
+    // statistics: one atomic per CTA and counter
+    __shared__ uint32_t s_stat[3];
+    if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
+    __syncthreads();
+    uint32_t f = __reduce_add_sync(FULL, finished), hv = __reduce_add_sync(FULL, have ? 1u : 0u),
+             sh = __reduce_add_sync(FULL, n_shade);
+    if (lane == 0) {
+      atomicAdd(&s_stat[0], f);
+      atomicAdd(&s_stat[1], hv);
+      atomicAdd(&s_stat[2], sh);
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+      atomicAdd(stats + ST_PATHS, (unsigned long long)s_stat[0]);
+      atomicAdd(stats + ST_SEGMENTS, (unsigned long long)s_stat[1]);
+      atomicAdd(stats + ST_SHADE, (unsigned long long)s_stat[2]);
+    }
   }
 }
 
