@@ -151,3 +151,31 @@ def test_kernel_variants_agree_on_generated_meshes(ctx, name, w, h, spp, tmp_pat
     hs = host.HostScene(gen_scenes.generate(d, [name])[name])
     st = _variants_agree(ctx, hs.desc(), hs.camera(), w, h, spp)
     assert st["n_tritest"] < st["n_tri"]  # and it must actually skip work
+
+
+@pytest.mark.parametrize("w,h,spp,tune", [(3, 5, 1, None), (17, 9, 33, None), (64, 40, 5, (1 << 8) | 8),
+                                          (200, 120, 3, (256 << 8) | 8), (200, 120, 3, (256 << 8) | 32 | 8)])
+def test_wavefront_pool_edge_cases(w, h, spp, tune, monkeypatch):
+    """The wavefront pipeline against the megakernel on films smaller than a tile, pools far
+    smaller than the path count (FS2_TUNE bits 8..: 1 024 paths -> hundreds of waves, one and two
+    pipes) and padded tile grids: same paths, same film up to summation order, same aux."""
+    import fs2_b200
+    if tune is not None:
+        monkeypatch.setenv("FS2_TUNE", str(tune))
+    g = golden("mesh_tiny")
+    with fs2_b200.Context(device=0, stats=True) as c:
+        c.upload(g.scene)
+        c.resize(w, h)
+        out = []
+        for flags in (fs2_b200.FS_TRACE_MEGAKERNEL, fs2_b200.FS_TRACE_DEFAULT):
+            c.reset()
+            c.reset_stats()
+            c.trace(g.cam, spp, seed=21, flags=flags)
+            out.append((c.read_film(aux=True), c.stats()))
+    (fm, sm), (fw, sw) = out
+    assert (fw["count"] == spp).all()
+    assert np.allclose(fw["mean"], fm["mean"], rtol=4e-7 * spp, atol=1e-7)
+    assert (fw["normal"].view(np.uint32) == fm["normal"].view(np.uint32)).all()
+    assert (fw["mat_id"] == fm["mat_id"]).all()
+    for k in ("n_paths", "n_segments", "n_node", "n_tri", "n_prim", "n_shade"):
+        assert sm[k] == sw[k], k
