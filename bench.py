@@ -167,6 +167,14 @@ KERNEL_NAME = ["k_trace_phase<0>"]
 
 
 # --------------------------------------------------------------------------- roofline
+# DRAM bytes of one launch of each wavefront kernel on a full 4 194 304-path wave of the bench
+# scene: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture each
+# (profiles/r1_h_wf_trace_ncu_full_details.txt: 279.2 + 53.2 MB; r1_h_wf_shade_...: 526.6 + 321.3 MB).
+# Per ray segment that is 281 B, against the ~212 B of path state + hit record the pipeline moves
+# by design; the scene itself is served from L2.
+PROFILED_DRAM_BYTES_PER_SEGMENT = (279.206656e6 + 53.182208e6 + 526.639360e6 + 321.259008e6) / 4194304.0
+
+
 def roofline(ctx_stats, objects, n_pixels, kernel_ms, peaks):
     """Algorithmic bytes / flops per SURVEY.md §8(d) from the stats-build counters of one
     launch, against the measured HBM peak and the FP32 pipe peak."""
@@ -332,6 +340,10 @@ def run_gpu(args, rank, world, local_rank):
                                 .from_address(desc.objects), dtype=abi.OBJECT_DT)
         kms = sum(kernel_ms) / len(kernel_ms)
         roof = roofline(sst, objects, n_px, kms, peaks)
+        if args.variant == "wavefront":
+            roof["traffic"] = PROFILED_DRAM_BYTES_PER_SEGMENT * sst["n_segments"]
+            roof["traffic_source"] = ("ncu --set full, one k_wf_trace + one k_wf_shade launch on a full "
+                                      "wave (profiles/r1_h_*), scaled by this run's ray segments")
         try:
             cpu = cpu_sample(scene_file) if (world == 1 and not args.skip_cpu) else None
         except Exception as e:  # the reference binary did not travel
