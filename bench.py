@@ -296,20 +296,32 @@ def run_gpu(args, rank, world, local_rank):
     paths = float(WIDTH) * HEIGHT * SPP * args.steps
     value = paths / total_ms / 1e3
 
-    # ---- e2e through the host mirror (TraceSamples: camera in, host film out), N ranks
+    # ---- e2e: camera (host POD) in, image in host buffers out on rank 0.
+    #  N = 1: through the host mirror of the reference API (TraceSamples = n x TraceScene).
+    #  N > 1: every rank calls the C ABI (fs_trace on its sample shard), the films are summed on
+    #         the device (NCCL reduce to rank 0), rank 0 resolves and reads the film back through
+    #         fs_film_read (mean, count, rgb8, normal, depth, material id: 81 MB D2H).
     frame = host.HostFrame(WIDTH, HEIGHT)
     hs.lib.fs2h_set_device(local_rank)
     e2e_s = []
+    host_film = {}
+    if world > 1 and rank == 0:
+        from fs2_b200 import engine
+        host_film = {"mean": np.empty((WIDTH * HEIGHT, 3), np.float32), "count": np.empty(WIDTH * HEIGHT, np.uint32),
+                     "rgb8": np.empty((WIDTH * HEIGHT, 3), np.uint8), "normal": np.empty((WIDTH * HEIGHT, 3), np.float32),
+                     "depth": np.empty(WIDTH * HEIGHT, np.float32), "mat_id": np.empty(WIDTH * HEIGHT, np.uint64)}
+        for a in host_film.values():
+            engine.pin_host(a)  # caller-owned, page-locked result buffers
     for i in range(1 + max(1, min(args.steps, 2))):
-        frame.reset()
         barrier()
         t0 = time.perf_counter()
-        frame.trace(hs, cam, n_mine)
-        if world > 1:
-            # host films are combined on rank 0: sum = mean * count
-            part = torch.from_numpy(frame.mean() * frame.count()[:, None].astype(np.float32)).cuda()
-            dist.reduce(part, 0)
-            part.cpu()
+        if world == 1:
+            frame.reset()
+            frame.trace(hs, cam, n_mine)
+        else:
+            multi_gpu.render_sharded(ctx, cam, SPP, SEED + 2000 + i, rank, world, flags=variant)
+            if rank == 0:
+                ctx.read_film(aux=True, out=host_film)
         barrier()
         e2e_s.append(time.perf_counter() - t0)
     e2e_t = torch.tensor([min(e2e_s[1:])], dtype=torch.float64, device="cuda")

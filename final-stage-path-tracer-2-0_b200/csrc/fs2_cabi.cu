@@ -53,7 +53,7 @@ struct fs_ctx {
   uint32_t n_nodes = 0, n_tris = 0, n_faces = 0, n_materials = 0;
   // film
   int width = 0, height = 0;
-  DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch;
+  DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch, auxpack;
   DeviceBuf wf_planes, wf_hit, wf_counters;  // wavefront path state
   uint32_t* wf_host_live = nullptr;   // pinned: live paths of the newest wave, per pipe
   cudaEvent_t wf_events[FS2_WF_AHEAD * FS2_WF_PIPES] = {};
@@ -413,7 +413,7 @@ int fs_destroy(fs_ctx* ctx) {
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
                       &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
-                      &ctx->scratch, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters};
+                      &ctx->scratch, &ctx->auxpack, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters};
   for (DeviceBuf* b : all) dev_free(b);
   if (ctx->d_stats) cudaFree(ctx->d_stats);
   if (ctx->wf_host_live) {
@@ -673,26 +673,41 @@ int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8, f
   if (mean_rgb) CUDA_TRY(ctx, cudaMemcpyAsync(mean_rgb, ctx->mean.p, n * 12, cudaMemcpyDeviceToHost, ctx->stream));
   if (count) CUDA_TRY(ctx, cudaMemcpyAsync(count, ctx->count.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
   if (rgb8) CUDA_TRY(ctx, cudaMemcpyAsync(rgb8, ctx->rgb8.p, n * 3, cudaMemcpyDeviceToHost, ctx->stream));
-  std::vector<float> aux;
-  std::vector<uint32_t> ids;
-  if (normal || depth) {
-    aux.resize(n * 4);
-    CUDA_TRY(ctx, cudaMemcpyAsync(aux.data(), ctx->aux.p, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
-  }
-  if (mat_id) {
-    ids.resize(n);
-    CUDA_TRY(ctx, cudaMemcpyAsync(ids.data(), ctx->mat_id.p, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+  if (normal || depth || mat_id) {
+    // split the aux planes on the device into the caller's layouts, then copy straight into
+    // the caller's buffers (full-speed DMA when they are page-locked, see fs_host_register)
+    if ((rc = dev_alloc(ctx, &ctx->auxpack, n * 24))) return rc;
+    unsigned long long* d_ids = (unsigned long long*)ctx->auxpack.p;
+    float* d_normal = (float*)(d_ids + n);
+    float* d_depth = d_normal + 3 * n;
+    k_unpack_aux<<<(unsigned)((n + 255) / 256), 256, 0, ctx->stream>>>(
+        (const float4*)ctx->aux.p, (const uint32_t*)ctx->mat_id.p, (int)n, d_normal, d_depth, d_ids);
+    ctx->launches++;
+    if (normal) CUDA_TRY(ctx, cudaMemcpyAsync(normal, d_normal, n * 12, cudaMemcpyDeviceToHost, ctx->stream));
+    if (depth) CUDA_TRY(ctx, cudaMemcpyAsync(depth, d_depth, n * 4, cudaMemcpyDeviceToHost, ctx->stream));
+    if (mat_id) CUDA_TRY(ctx, cudaMemcpyAsync(mat_id, d_ids, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
-  for (size_t i = 0; i < n && (normal || depth); i++) {
-    if (normal) {
-      normal[3 * i] = aux[4 * i];
-      normal[3 * i + 1] = aux[4 * i + 1];
-      normal[3 * i + 2] = aux[4 * i + 2];
-    }
-    if (depth) depth[i] = aux[4 * i + 3];
+  return FS_OK;
+}
+
+int fs_host_register(void* p, size_t bytes) {
+  if (!p || !bytes) return fail(nullptr, FS_E_INVALID, "fs_host_register: null buffer");
+  cudaError_t e = cudaHostRegister(p, bytes, cudaHostRegisterPortable);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(nullptr, FS_E_CUDA, "cudaHostRegister: %s", cudaGetErrorString(e));
   }
-  for (size_t i = 0; i < n && mat_id; i++) mat_id[i] = ids[i];
+  return FS_OK;
+}
+
+int fs_host_unregister(void* p) {
+  if (!p) return FS_OK;
+  cudaError_t e = cudaHostUnregister(p);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(nullptr, FS_E_CUDA, "cudaHostUnregister: %s", cudaGetErrorString(e));
+  }
   return FS_OK;
 }
 

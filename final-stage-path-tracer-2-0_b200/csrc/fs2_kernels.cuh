@@ -404,6 +404,21 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
 #include "fs2_wavefront.cuh"
 namespace fs2 {
 
+// aux planes -> the layouts DisplayFrame exposes (frame.h:86-91): normal[3], depth, 64-bit id
+__global__ void __launch_bounds__(256)
+k_unpack_aux(const float4* __restrict__ aux, const uint32_t* __restrict__ ids, int n,
+             float* __restrict__ normal, float* __restrict__ depth,
+             unsigned long long* __restrict__ id64) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  float4 a = aux[i];
+  normal[3 * i + 0] = a.x;
+  normal[3 * i + 1] = a.y;
+  normal[3 * i + 2] = a.z;
+  depth[i] = a.w;
+  id64[i] = ids[i];
+}
+
 // reference source/frame.cpp:56-69: mean and display RGB8 = 255*pow(sat(mean), 1/2.2) + 0.5
 __global__ void __launch_bounds__(256)
 k_resolve(const float4* __restrict__ sum, int n, float* __restrict__ mean_rgb,

@@ -9,6 +9,8 @@ from . import abi, build
 
 _SYMBOLS = {
     "fs_abi_version": (C.c_int, []),
+    "fs_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
+    "fs_host_unregister": (C.c_int, [C.c_void_p]),
     "fs_mesh_tree_build": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
                                      C.c_uint32, C.c_uint32, C.c_uint32, C.c_uint32,
                                      C.POINTER(abi.fs_mesh_tree)]),
@@ -66,6 +68,20 @@ def load_library(path=None):
 
 def exported_symbols():
     return sorted(_SYMBOLS)
+
+
+def pin_host(array):
+    """Page-locks a numpy array in place (fs_host_register) so film read-backs into it run at
+    full PCIe speed; returns the array.  Call unpin_host before the array is freed."""
+    lib = load_library()
+    rc = lib.fs_host_register(array.ctypes.data_as(C.c_void_p), array.nbytes)
+    if rc != 0:
+        raise RuntimeError("fs_host_register: %s" % lib.fs_last_error(None).decode())
+    return array
+
+
+def unpin_host(array):
+    load_library().fs_host_unregister(array.ctypes.data_as(C.c_void_p))
 
 
 def _ptr(a):

@@ -93,9 +93,28 @@ DisplayFrame::DisplayFrame(uint32 width, uint32 height) : impl_(new FrameImpl())
   f.count.assign(n, 0);
   f.rgb8.assign(n * 3, 0);
   f.mat_id.assign(n, 0);
+  // page-lock the film so fs_film_read lands in it by DMA; without a device this fails and the
+  // buffers simply stay pageable
+  f.pinned = n > 0 && fs_host_register(f.mean.data(), n * 12) == FS_OK;
+  if (f.pinned) {
+    fs_host_register(f.normal.data(), n * 12);
+    fs_host_register(f.depth.data(), n * 4);
+    fs_host_register(f.count.data(), n * 4);
+    fs_host_register(f.rgb8.data(), n * 3);
+    fs_host_register(f.mat_id.data(), n * 8);
+  }
 }
 DisplayFrame::~DisplayFrame() {
   if (state().frame == impl_.get()) state().frame = nullptr;
+  FrameImpl& f = *impl_;
+  if (f.pinned) {
+    fs_host_unregister(f.mean.data());
+    fs_host_unregister(f.normal.data());
+    fs_host_unregister(f.depth.data());
+    fs_host_unregister(f.count.data());
+    fs_host_unregister(f.rgb8.data());
+    fs_host_unregister(f.mat_id.data());
+  }
 }
 void DisplayFrame::Reset() {  // frame.cpp:43-51
   FrameImpl& f = *impl_;

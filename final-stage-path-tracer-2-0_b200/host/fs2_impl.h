@@ -55,6 +55,7 @@ struct FrameImpl {
   std::vector<uint64_t> mat_id;
   uint32_t samples = 0;  // samples accumulated since the last Reset()
   bool device_dirty = true;  // device film must be cleared before the next launch
+  bool pinned = false;       // buffers are page-locked (fs_host_register)
 };
 
 inline Vec3 to3(const base::vector3& v) { return Vec3(v.x, v.y, v.z); }

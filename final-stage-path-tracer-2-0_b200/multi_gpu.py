@@ -6,13 +6,18 @@ import torch.distributed as dist
 
 
 def shard_samples(total, rank, world):
-    """Rank r renders samples {r, r + world, ...} of every pixel.  Returns (first_sample,
-    n_samples, stride); per-sample random streams depend only on (seed, pixel, sample
-    index), so the union over ranks is exactly the single-GPU sample set."""
+    """Rank r renders the samples congruent to (total - 1 - r) modulo world of every pixel, so
+    rank 0 — where the film is resolved and read — owns the last sample, whose depth-0 hit fills
+    the aux buffers (reference frame.cpp:78-85: last sample wins).  Returns (first_sample,
+    n_samples, stride); per-sample random streams depend only on (seed, pixel, sample index),
+    so the union over ranks is exactly the single-GPU sample set."""
     if world <= 0 or not 0 <= rank < world or total < 0:
         raise ValueError("bad shard request")
-    n = (total - rank + world - 1) // world if total > rank else 0
-    return rank, n, world
+    if total == 0:
+        return 0, 0, world
+    first = (total - 1 - rank) % world
+    n = (total - first + world - 1) // world if total > first else 0
+    return first, n, world
 
 
 class _DevicePtr:

@@ -277,6 +277,11 @@ int fs_film_resolve(fs_ctx* ctx);
 int fs_get_stats(fs_ctx* ctx, fs_stats* out);
 int fs_reset_stats(fs_ctx* ctx);
 
+/* Page-locks / releases a caller-owned host buffer (cudaHostRegister) so that fs_film_read and
+ * fs_first_hit copy into it by DMA at full PCIe speed; optional, any host pointer works. */
+int fs_host_register(void* buffer, size_t bytes);
+int fs_host_unregister(void* buffer);
+
 /* CUDA stream the context launches on (cudaStream_t as void*).  fs_set_stream makes the
  * context enqueue on a caller-owned stream (e.g. the one an NCCL reduce of the film runs
  * on); NULL restores the context's own stream. */

@@ -22,6 +22,10 @@ def test_shard_samples_partitions_exactly():
             assert sorted(seen) == list(range(total))
             sizes = [multi_gpu.shard_samples(total, r, world)[1] for r in range(world)]
             assert max(sizes) - min(sizes) <= 1
+            if total:
+                # rank 0 owns the last sample: its aux buffers are the image's (last sample wins)
+                first, n, stride = multi_gpu.shard_samples(total, 0, world)
+                assert first + (n - 1) * stride == total - 1
 
 
 def _worker(rank, world, port, out_dir):
