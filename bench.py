@@ -293,6 +293,26 @@ def run_gpu(args, rank, world, local_rank):
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(segs, op=dist.ReduceOp.SUM)
     total_ms = float(total_ms.item())
+    # BASELINE.json's second figure: time to image at 1080p, 256 spp (one extra, separately
+    # timed frame; not part of `value`)
+    f256, n256, s256 = multi_gpu.shard_samples(256, rank, world)
+    flush.zero_()
+    barrier()
+    e0 = torch.cuda.Event(enable_timing=True)
+    e1 = torch.cuda.Event(enable_timing=True)
+    e0.record()
+    ctx.reset()
+    ctx.trace(cam, n256, first_sample=f256, stride=s256, seed=SEED + 5000, flags=flags)
+    if world > 1:
+        multi_gpu.reduce_film(film, 0)
+    if rank == 0:
+        ctx.resolve()
+    e1.record()
+    barrier()
+    t256 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(t256, op=dist.ReduceOp.MAX)
+    t256 = float(t256.item())
     paths = float(WIDTH) * HEIGHT * SPP * args.steps
     value = paths / total_ms / 1e3
 
@@ -372,6 +392,7 @@ def run_gpu(args, rank, world, local_rank):
                            "l2": "flushed between steps (256 MiB write)", "seed": SEED,
                            "variant": args.variant,
                            "time_to_image_ms": total_ms / args.steps,
+                           "time_to_image_1080p_256spp_ms": t256,
                            "mrays_per_s": float(segs.item()) / total_ms / 1e3},
                 "clocks": sampler.summary(), "roofline": roof,
                 "e2e": {"value": e2e_value, "unit": "Mpaths/s", "h2d_bytes_per_step": 48,
