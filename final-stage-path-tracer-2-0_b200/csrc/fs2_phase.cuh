@@ -428,4 +428,106 @@ __device__ __forceinline__ void ph_lb_tris(const DScene& S, PhLane& w, const Ray
   if (!w.qmask) ph_lb_pop(w, S, sm);
 }
 
+// Warp-cooperative form of ph_lb_tris, called by the whole (converged) warp.  `owners` = lanes
+// in PH_LB_TRIS.  ncu (profiles/r1_h): the per-lane form ran at 6 of 32 lanes and was 26 % of the
+// traversal kernel's instructions.  Here every owner's group of <= 4 records is spread over 4
+// lanes: up to 8 owners per pass, one record per lane — plane stage, acceptance filter and
+// barycentric stage all run once, in parallel, and a 4-lane (t, leaf rank) min-reduction picks
+// the record the sequential loop would have kept:
+//   sequential rule (lb_test_tris): accept when inside and (t < bt, or t == bt and a record of
+//   this leaf is already held and rank < its rank); the survivor of a group is therefore the
+//   lexicographic minimum (t, rank) over the records that pass that test against the state the
+//   group started with.
+// slot_owner: 8 bytes of shared memory per warp.
+template <bool STATS>
+__device__ __forceinline__ void ph_lb_tris_coop(const DScene& S, PhLane& w, const Ray& r,
+                                                const PhSmem& sm, Counters& c, unsigned owners,
+                                                volatile uint8_t* slot_owner) {
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int lane = threadIdx.x & 31;
+  const unsigned below = (1u << lane) - 1u;
+  const bool own = (owners >> lane) & 1u;
+  uint32_t k0 = 0, n = 0;
+  if (own) {
+    uint32_t g = (uint32_t)__ffs((int)w.qmask) - 1u;
+    w.qmask &= w.qmask - 1u;
+    uint32_t rem = w.qcount - 4u * g;
+    n = rem < 4u ? rem : 4u;
+    k0 = w.qbase + 4u * g;
+    if (STATS) c.n_tritest += n;
+    if (w.qmask) prefetch_l1(S.lb_plane + w.qbase + 4u * ((uint32_t)__ffs((int)w.qmask) - 1u));
+  }
+  unsigned todo = owners;
+  while (todo) {
+    // the first 8 owners take the 8 four-lane slots
+    const uint32_t rank = (uint32_t)__popc(todo & below);
+    const bool served = ((todo >> lane) & 1u) && rank < 8u;
+    if (served) slot_owner[rank] = (uint8_t)lane;
+    __syncwarp();
+    const uint32_t n_served = min((uint32_t)__popc(todo), 8u);
+    const uint32_t slot = (uint32_t)lane >> 2, j = (uint32_t)lane & 3u;
+    const int src = slot < n_served ? (int)slot_owner[slot] : 0;
+    __syncwarp();
+    const uint32_t ko = __shfl_sync(FULL, k0, src), no = __shfl_sync(FULL, n, src);
+    const V3 s = v3(__shfl_sync(FULL, r.start.x, src), __shfl_sync(FULL, r.start.y, src),
+                    __shfl_sync(FULL, r.start.z, src));
+    const V3 d = v3(__shfl_sync(FULL, r.dir.x, src), __shfl_sync(FULL, r.dir.y, src),
+                    __shfl_sync(FULL, r.dir.z, src));
+    const float bt = __shfl_sync(FULL, w.bt, src);
+    const uint32_t border = __shfl_sync(FULL, w.border, src);
+    const bool found = __shfl_sync(FULL, w.flags & PH_F_FOUND, src) != 0u;
+    float kt = FS2_INFINITY, u = 0.f, v = 0.f;
+    uint32_t kord = 0xFFFFFFFFu;
+    if (slot < n_served && j < no) {
+      const uint32_t k = ko + j;
+      float4 pl = __ldg(S.lb_plane + k);
+      float ts = pl.x * d.x + pl.y * d.y + pl.z * d.z;
+      if (!near_zero(ts)) {
+        float ns = -(pl.x * s.x + pl.y * s.y + pl.z * s.z + pl.w);
+        float t = ns / ts;
+        if (t >= 0.0f && t <= 1.0f && (t < bt || (t == bt && found))) {
+          uint32_t ord = __ldg(S.lb_order + k);
+          if (t < bt || ord < border) {
+            if (STATS) c.n_bary++;
+            float uu, vv;
+            if (tri_inside(S.lb_aux + 3 * (size_t)k, s + d * t, uu, vv)) {
+              kt = t;
+              kord = ord;
+              u = uu;
+              v = vv;
+            }
+          }
+        }
+      }
+    }
+#pragma unroll
+    for (int off = 1; off <= 2; off <<= 1) {
+      float ot = __shfl_xor_sync(FULL, kt, off);
+      uint32_t oo = __shfl_xor_sync(FULL, kord, off);
+      float ou = __shfl_xor_sync(FULL, u, off), ov = __shfl_xor_sync(FULL, v, off);
+      if (ot < kt || (ot == kt && oo < kord)) {
+        kt = ot;
+        kord = oo;
+        u = ou;
+        v = ov;
+      }
+    }
+    // hand the slot's winner back to its owner
+    const int from = served ? (int)(4u * rank) : 0;
+    const float rt = __shfl_sync(FULL, kt, from);
+    const uint32_t ro = __shfl_sync(FULL, kord, from);
+    const float ru = __shfl_sync(FULL, u, from), rv = __shfl_sync(FULL, v, from);
+    if (served && ro != 0xFFFFFFFFu) {
+      w.bt = rt;
+      w.border = ro;
+      w.bu = ru;
+      w.bv = rv;
+      w.flags |= PH_F_FOUND;
+    }
+    const unsigned served_mask = __ballot_sync(FULL, served);
+    todo &= ~served_mask;
+  }
+  if (own && !w.qmask) ph_lb_pop(w, S, sm);
+}
+
 }  // namespace fs2

@@ -188,6 +188,9 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #ifndef FS2_WF_REP_RETURN
 #define FS2_WF_REP_RETURN 4
 #endif
+#ifndef FS2_WF_COOP_TRIS
+#define FS2_WF_COOP_TRIS 1  // triangle groups tested by 4 lanes each (ph_lb_tris_coop)
+#endif
 #ifndef FS2_WF_MIN_BLOCKS
 #define FS2_WF_MIN_BLOCKS 6  // measured (no scene tree, Mpaths/s): 5 -> 400 (92 regs), 6 -> 433 (80 regs, 12 B spilled), 7 -> 434, 8 -> 398
 #endif
@@ -197,6 +200,7 @@ template <bool STATS, bool TREE>
 __global__ void __launch_bounds__(FS2_PH_THREADS, FS2_WF_MIN_BLOCKS)
 k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict__ stats) {
   extern __shared__ uint32_t ph_smem[];
+  __shared__ uint8_t s_slot_owner[FS2_PH_THREADS / 32][8];
   PhSmem sm;
   sm.col = ph_smem + threadIdx.x;
   const unsigned FULL = 0xFFFFFFFFu;
@@ -263,7 +267,16 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
     FS2_PHASE_N(PH_OBJ, FS2_WF_REP_OBJ, FS2_WF_REPEAT_MIN, (ph_object<STATS, TREE>(S, w, ray, c)))
     FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, (ph_enter<STATS, TREE>(S, w, ray, sm, c)))
     FS2_PHASE_N(PH_LB_NODE, FS2_WF_REP_NODE, FS2_WF_REPEAT_MIN, ph_lb_node<STATS>(S, w, ray, q, sm, c))
+#if FS2_WF_COOP_TRIS
+#pragma unroll 1
+    for (int rep_ = 0; rep_ < FS2_WF_REP_TRIS; ++rep_) {
+      unsigned m_ = __ballot_sync(FULL, w.st == PH_LB_TRIS);
+      if (!m_ || (rep_ && __popc(m_) < FS2_WF_REPEAT_MIN)) break;
+      ph_lb_tris_coop<STATS>(S, w, ray, sm, c, m_, s_slot_owner[threadIdx.x >> 5]);
+    }
+#else
     FS2_PHASE_N(PH_LB_TRIS, FS2_WF_REP_TRIS, FS2_WF_REPEAT_MIN, ph_lb_tris<STATS>(S, w, ray, sm, c))
+#endif
     FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, ph_return<TREE>(S, w, ray, sm))
     if (w.st == PH_SHADE) {  // nearest hit of the segment is final
       wf_store_hit(B, idx, w.rec);
