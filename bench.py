@@ -169,7 +169,8 @@ KERNEL_NAME = ["k_trace_phase<0>"]
 # --------------------------------------------------------------------------- roofline
 # DRAM bytes of one launch of each wavefront kernel on a full 4 194 304-path wave of the bench
 # scene: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture each
-# (profiles/r1_h_wf_trace_ncu_full_details.txt: 279.2 + 53.2 MB; r1_h_wf_shade_...: 526.6 + 321.3 MB).
+# (profiles/r1_h_wf_trace_ncu_full_details.txt: 279.2 + 53.2 MB; r1_h_wf_shade_...: 526.6 + 321.3 MB;
+# unchanged in r1_j: 280.3 + 52.6 and 526.7 + 322.2 MB).
 # Per ray segment that is 281 B, against the ~212 B of path state + hit record the pipeline moves
 # by design; the scene itself is served from L2.
 PROFILED_DRAM_BYTES_PER_SEGMENT = (279.206656e6 + 53.182208e6 + 526.639360e6 + 321.259008e6) / 4194304.0
