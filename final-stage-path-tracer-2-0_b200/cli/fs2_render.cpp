@@ -2,7 +2,8 @@
 // path (reference source/main.cpp:47-168 opens a Win32/OpenGL window, which is unavailable
 // on this box).  Same options (-f file, -w width, -h height; first-letter matching like
 // source/main.cpp:61-76) plus --spp, --seed, --device, --out, --focus x,y (the click-to-focus
-// of source/main.cpp:144-153 through TraceRange) and --fast (Camera::fast_render_enabled).
+// of source/main.cpp:144-153 through TraceRange), --fast (Camera::fast_render_enabled) and
+// --checkpoint / --resume (the accumulation film on disk: a render continues where it stopped).
 // Written against the mirrored API of host/fs2_host.h only.
 //
 //   fs2_render -f scene.scene -w 1920 -h 1080 --spp 64 --out image.ppm [--pfm mean.pfm]
@@ -40,7 +41,7 @@ static bool write_pfm(const std::string& path, DisplayFrame* f) {
 }
 
 int main(int argc, char** argv) {
-  std::string file, out = "fs2_render.ppm", pfm;
+  std::string file, out = "fs2_render.ppm", pfm, checkpoint, resume;
   uint32 width = 800, height = 480, spp = 16;  // 800x480: source/main.cpp:53-54
   uint64 seed = 1;
   int device = 0;
@@ -55,6 +56,8 @@ int main(int argc, char** argv) {
     else if (!strcmp(a, "--out")) out = next();
     else if (!strcmp(a, "--pfm")) pfm = next();
     else if (!strcmp(a, "--fast")) fast = true;
+    else if (!strcmp(a, "--checkpoint")) checkpoint = next();
+    else if (!strcmp(a, "--resume")) resume = next();
     else if (!strcmp(a, "--focus")) have_focus = sscanf(next(), "%f,%f", &fx, &fy) == 2;
     else if (a[0] == '-' && (a[1] == 'f' || (a[1] == '-' && a[2] == 'f'))) file = next();
     else if (a[0] == '-' && (a[1] == 'w' || (a[1] == '-' && a[2] == 'w'))) width = (uint32)atoi(next());
@@ -66,7 +69,8 @@ int main(int argc, char** argv) {
   }
   if (file.empty()) {  // source/main.cpp:78-81
     fprintf(stderr, "usage: fs2_render -f <scene file> [-w W] [-h H] [--spp N] [--seed S] "
-                    "[--device D] [--out image.ppm] [--pfm mean.pfm] [--focus x,y] [--fast]\n");
+                    "[--device D] [--out image.ppm] [--pfm mean.pfm] [--focus x,y] [--fast] "
+                    "[--resume film.ckpt] [--checkpoint film.ckpt]\n");
     return 2;
   }
   Scene scene;
@@ -84,6 +88,10 @@ int main(int argc, char** argv) {
     cam.focal_depth = TraceRange(cam, &scene, &frame, fx, fy);
     printf("focal depth at (%.1f, %.1f): %.4f\n", fx, fy, cam.focal_depth);
   }
+  if (!resume.empty() && !LoadFilmCheckpoint(&frame, resume.c_str())) {
+    fprintf(stderr, "cannot resume from %s: %s\n", resume.c_str(), LastTraceError());
+    return 1;
+  }
   auto t0 = std::chrono::steady_clock::now();
   if (TraceSamples(cam, &scene, &frame, spp) != 0) {
     fprintf(stderr, "render failed: %s\n", LastTraceError());
@@ -92,6 +100,10 @@ int main(int argc, char** argv) {
   double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
   printf("%ux%u, %u spp in %.3f s (%.2f Mpaths/s, scene upload included)\n", width, height, spp,
          sec, (double)width * height * spp / sec / 1e6);
+  if (!checkpoint.empty() && !SaveFilmCheckpoint(&frame, checkpoint.c_str())) {
+    fprintf(stderr, "cannot write %s: %s\n", checkpoint.c_str(), LastTraceError());
+    return 1;
+  }
   if (!write_ppm(out, &frame)) {
     fprintf(stderr, "cannot write %s\n", out.c_str());
     return 1;

@@ -719,6 +719,27 @@ int fs_film_device(fs_ctx* ctx, void** sum_rgba, size_t* n_floats) {
   return FS_OK;
 }
 
+int fs_film_save(fs_ctx* ctx, float* sum_rgba) {
+  if (!ctx || !sum_rgba) return fail(ctx, FS_E_INVALID, "null argument");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_save before fs_film_resize");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  size_t n = (size_t)ctx->width * ctx->height;
+  CUDA_TRY(ctx, cudaMemcpyAsync(sum_rgba, ctx->sum.p, n * 16, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_film_load(fs_ctx* ctx, const float* sum_rgba) {
+  if (!ctx || !sum_rgba) return fail(ctx, FS_E_INVALID, "null argument");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_load before fs_film_resize");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  size_t n = (size_t)ctx->width * ctx->height;
+  CUDA_TRY(ctx, cudaMemcpyAsync(ctx->sum.p, sum_rgba, n * 16, cudaMemcpyHostToDevice, ctx->stream));
+  return fs_film_resolve(ctx);
+}
+
 int fs_get_stats(fs_ctx* ctx, fs_stats* out) {
   if (!ctx || !out) return fail(ctx, FS_E_INVALID, "null argument");
   int rc = set_device(ctx);

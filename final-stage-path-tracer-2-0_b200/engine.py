@@ -9,6 +9,8 @@ from . import abi, build
 
 _SYMBOLS = {
     "fs_abi_version": (C.c_int, []),
+    "fs_film_save": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "fs_film_load": (C.c_int, [C.c_void_p, C.c_void_p]),
     "fs_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
     "fs_host_unregister": (C.c_int, [C.c_void_p]),
     "fs_mesh_tree_build": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
@@ -175,6 +177,17 @@ class Context:
                                           _ptr(film.get("normal")), _ptr(film.get("depth")),
                                           _ptr(film.get("mat_id"))))
         return film
+
+    def save_film(self):
+        """Accumulation film (rgb sum, count per pixel) as a numpy array: a checkpoint."""
+        a = np.empty((self.width * self.height, 4), np.float32)
+        self._check(self.lib.fs_film_save(self.handle, _ptr(a)))
+        return a
+
+    def load_film(self, sums):
+        a = np.ascontiguousarray(sums, np.float32)
+        assert a.size == self.width * self.height * 4
+        self._check(self.lib.fs_film_load(self.handle, _ptr(a)))
 
     def film_device(self):
         """(device pointer, float count) of the rgb-sum/count film for an external reduce."""

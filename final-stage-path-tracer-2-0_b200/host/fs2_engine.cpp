@@ -3,6 +3,9 @@
 // meets the C ABI: flatten-if-dirty -> fs_scene_upload -> fs_trace / fs_first_hit ->
 // fs_film_read into the DisplayFrame's host buffers.  No tracing happens on the host.
 #include <stdio.h>
+#include <string.h>
+
+#include <vector>
 
 #include "fs2_impl.h"
 #include "fs2_octree.h"
@@ -31,6 +34,12 @@ int fail(const char* what, fs_ctx* ctx) {
   snprintf(st.error, sizeof st.error, "%s: %s", what, fs_last_error(ctx));
   fprintf(stderr, "fs2: %s\n", st.error);
   return -1;
+}
+
+void fail_msg(const char* msg) {
+  TraceState& st = state();
+  snprintf(st.error, sizeof st.error, "%s", msg);
+  fprintf(stderr, "fs2: %s\n", st.error);
 }
 
 int ensure_context() {
@@ -172,6 +181,69 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
                    f->depth.data(), f->mat_id.data()) != FS_OK)
     return fail("fs_film_read", st.ctx);
   return 0;
+}
+
+namespace {
+struct CheckpointHeader {
+  char magic[8];  // "FS2FILM1"
+  uint32_t width, height, samples, reserved;
+};
+}  // namespace
+
+bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path) {
+  TraceState& st = state();
+  if (!frame || !path || !st.ctx || st.frame != frame->impl() || frame->impl()->device_dirty) {
+    fail_msg("SaveFilmCheckpoint: the frame has no samples on the device");
+    return false;
+  }
+  FrameImpl* f = frame->impl();
+  std::vector<float> sums((size_t)f->width * f->height * 4);
+  if (fs_film_save(st.ctx, sums.data()) != FS_OK) {
+    fail("fs_film_save", st.ctx);
+    return false;
+  }
+  FILE* fp = fopen(path, "wb");
+  if (!fp) return false;
+  CheckpointHeader h = {{'F', 'S', '2', 'F', 'I', 'L', 'M', '1'}, f->width, f->height, f->samples, 0};
+  bool ok = fwrite(&h, sizeof h, 1, fp) == 1 && fwrite(sums.data(), 4, sums.size(), fp) == sums.size();
+  return fclose(fp) == 0 && ok;
+}
+
+bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path) {
+  if (!frame || !path) return false;
+  TraceState& st = state();
+  FrameImpl* f = frame->impl();
+  FILE* fp = fopen(path, "rb");
+  if (!fp) return false;
+  CheckpointHeader h;
+  std::vector<float> sums((size_t)f->width * f->height * 4);
+  bool ok = fread(&h, sizeof h, 1, fp) == 1 && !memcmp(h.magic, "FS2FILM1", 8) &&
+            h.width == f->width && h.height == f->height &&
+            fread(sums.data(), 4, sums.size(), fp) == sums.size();
+  fclose(fp);
+  if (!ok) {
+    fail_msg("LoadFilmCheckpoint: not a checkpoint of this frame size");
+    return false;
+  }
+  if (ensure_context()) return false;
+  if (st.film_w != f->width || st.film_h != f->height) {
+    if (fs_film_resize(st.ctx, (int)f->width, (int)f->height) != FS_OK) {
+      fail("fs_film_resize", st.ctx);
+      return false;
+    }
+    st.film_w = f->width;
+    st.film_h = f->height;
+  }
+  if (fs_film_load(st.ctx, sums.data()) != FS_OK ||
+      fs_film_read(st.ctx, f->mean.data(), f->count.data(), f->rgb8.data(), nullptr, nullptr, nullptr) != FS_OK) {
+    fail("fs_film_load", st.ctx);
+    return false;
+  }
+  st.frame = f;
+  f->device_dirty = false;
+  f->samples = h.samples;
+  f->frame_count = h.samples;
+  return true;
 }
 
 void TraceScene(const Camera& view, Scene* scene, DisplayFrame* output, ImagePlaneCache*) {

@@ -262,6 +262,11 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
 void SetTraceDevice(int device);
 void SetTraceSeed(uint64 seed);
 const char* LastTraceError();
+// Film checkpoint / resume (headless replacement of keeping the window open): the accumulation
+// film of `frame` goes to / comes from `path`; after a load the next TraceScene / TraceSamples
+// call continues the sample sequence where the checkpoint stopped.
+bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path);
+bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path);
 
 }  // namespace base
 #endif

@@ -272,6 +272,12 @@ int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8,
  * w = sample count as float).  After an external reduce call fs_film_resolve
  * to refresh mean/rgb8. */
 int fs_film_device(fs_ctx* ctx, void** sum_rgba, size_t* n_floats);
+
+/* Film checkpoint / resume: copies the accumulation film (4 floats per pixel: rgb sum, sample
+ * count) to / from a host buffer of width*height*4 floats.  After fs_film_load the resolved
+ * buffers are current and the next fs_trace continues at first_sample = the loaded count. */
+int fs_film_save(fs_ctx* ctx, float* sum_rgba);
+int fs_film_load(fs_ctx* ctx, const float* sum_rgba);
 int fs_film_resolve(fs_ctx* ctx);
 
 int fs_get_stats(fs_ctx* ctx, fs_stats* out);

@@ -34,3 +34,26 @@ def test_cli_fails_loudly_on_missing_scene(tmp_path):
     exe = build.build_cli()
     r = subprocess.run([exe, "-f", str(tmp_path / "nope.scene")], capture_output=True, text=True)
     assert r.returncode != 0
+
+
+def test_cli_checkpoint_resume_continues_the_sample_sequence(tmp_path):
+    """3 spp + checkpoint, then resume + 5 spp in a new process == 8 spp in one go (same seed:
+    sample k has the same random stream either way)."""
+    exe = build.build_cli()
+    scene = gen_scenes.generate(str(tmp_path), ["demo"])["demo"]
+    common = [exe, "-f", scene, "-w", "80", "-h", "48", "--seed", "9"]
+    ck = str(tmp_path / "film.ckpt")
+
+    def run(extra, name):
+        pfm = str(tmp_path / (name + ".pfm"))
+        r = subprocess.run(common + extra + ["--out", str(tmp_path / (name + ".ppm")), "--pfm", pfm],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        return np.frombuffer(open(pfm, "rb").read()[len(b"PF\n80 48\n-1.0\n"):], np.float32)
+
+    whole = run(["--spp", "8"], "whole")
+    run(["--spp", "3", "--checkpoint", ck], "part")
+    resumed = run(["--spp", "5", "--resume", ck], "resumed")
+    assert np.allclose(whole, resumed, rtol=1e-5, atol=1e-6)
+    bad = subprocess.run(common + ["-w", "64", "--spp", "1", "--resume", ck], capture_output=True, text=True)
+    assert bad.returncode != 0  # a checkpoint of another frame size is refused
