@@ -187,6 +187,8 @@ int validate_scene(fs_ctx* ctx, const fs_scene_desc* s) {
       (s->n_faces && !s->faces) || (s->n_objects && !s->objects) || !s->materials ||
       (s->n_textures && (!s->textures || !s->texels)) || (s->n_scene_refs && !s->scene_refs))
     return fail(ctx, FS_E_INVALID, "null array with non-zero count");
+  if (s->n_nodes >= (1u << FS2_PH_NODE_BITS))
+    return fail(ctx, FS_E_INVALID, "more than 2^%d octree nodes", FS2_PH_NODE_BITS);
   if (s->scene_root >= 0 && (uint32_t)s->scene_root >= s->n_nodes)
     return fail(ctx, FS_E_INVALID, "scene_root %d out of range", s->scene_root);
   for (uint32_t i = 0; i < s->n_nodes; i++) {

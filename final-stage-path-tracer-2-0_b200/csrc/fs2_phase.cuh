@@ -16,12 +16,13 @@
 // are bit-identical (tests/test_gpu_image.py compares all variants).
 //
 // Per-lane stacks live in shared memory, one 4-byte column per thread (conflict-free):
-//   mesh-octree frames   FS2_PH_MESH_FRAMES x 8 words
+//   mesh-octree frames   FS2_PH_MESH_FRAMES x 5 words (node | state bits, three split-plane
+//                        parameters, the entry parameter the entry point is rebuilt from)
 //   leaf-BVH stack       FS2_PH_LB_STACK x 1 word: (node - leaf root) << 16 | bf16(entry t),
 //                        a leaf's tree has < 65 536 nodes (fs2_lbvh_build.h) and a truncated
 //                        entry parameter only makes the pop-time cull conservative
-//   scene-octree frames  FS2_PH_SCENE_FRAMES x 8 words, allocated only when the scene has a
-//                        tree (>= 182 objects): 200 B instead of 360 B per lane otherwise, which
+//   scene-octree frames  FS2_PH_SCENE_FRAMES x 5 words, allocated only when the scene has a
+//                        tree (>= 182 objects): 152 B instead of 252 B per lane otherwise, which
 //                        is what bounds the CTAs per SM (and what is left for L1)
 #pragma once
 #include "fs2_shade.cuh"
@@ -32,8 +33,10 @@ namespace fs2 {
 #define FS2_PH_MESH_FRAMES 4   // mesh trees: internal nodes at depth 0..3 (mesh.cpp:16)
 #define FS2_PH_SCENE_FRAMES 5  // scene trees: internal nodes at depth 0..4 (<= ~2 M objects)
 #define FS2_PH_LB_STACK 18     // 6 inner leaf-BVH levels x 3 pending siblings
-#define FS2_PH_SLOTS_NOTREE (FS2_PH_MESH_FRAMES * 8 + FS2_PH_LB_STACK)
-#define FS2_PH_SLOTS (FS2_PH_SLOTS_NOTREE + FS2_PH_SCENE_FRAMES * 8)
+#define FS2_PH_FRAME_WORDS 5    // node | bits << 25, tx, ty, tz, entry parameter
+#define FS2_PH_NODE_BITS 25     // octree node indices below 2^25 (checked by fs_scene_upload)
+#define FS2_PH_SLOTS_NOTREE (FS2_PH_MESH_FRAMES * FS2_PH_FRAME_WORDS + FS2_PH_LB_STACK)
+#define FS2_PH_SLOTS (FS2_PH_SLOTS_NOTREE + FS2_PH_SCENE_FRAMES * FS2_PH_FRAME_WORDS)
 #define FS2_PH_SMEM_BYTES (FS2_PH_SLOTS * FS2_PH_THREADS * 4)
 // dynamic shared memory of a phase-machine kernel for a scene with / without a scene tree
 static inline unsigned ph_smem_bytes(bool scene_tree) {
@@ -90,12 +93,15 @@ struct PhSmem {
   }
   // word i of frame sp: mesh frames first, then the leaf-BVH stack, scene frames last
   __device__ __forceinline__ int fslot(bool mesh, int sp, int i) const {
-    return (mesh ? 0 : FS2_PH_SLOTS_NOTREE) + sp * 8 + i;
+    return (mesh ? 0 : FS2_PH_SLOTS_NOTREE) + sp * FS2_PH_FRAME_WORDS + i;
   }
-  __device__ __forceinline__ int lslot(int sp) const { return FS2_PH_MESH_FRAMES * 8 + sp; }
+  __device__ __forceinline__ int lslot(int sp) const {
+    return FS2_PH_MESH_FRAMES * FS2_PH_FRAME_WORDS + sp;
+  }
 };
 
-// frame words: 0 node, 1 bits, 2..4 tx ty tz, 5..7 sx sy sz   (struct Frame, fs2_traverse.cuh)
+// frame words: 0 node | bits << 25 (bits: 0-2 child, 3-4 visits, 5 returned a hit, 6 origin
+// inside), 1..3 tx ty tz, 4 entry parameter
 
 // Begin Scene::Trace for the lane's next ray (scene.cpp:227-237).
 // (TREE = false in the ph_* steps: the caller knows the scene has no scene octree, so the
@@ -189,16 +195,14 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
   V3 st = inside ? r.start : entry;
   uint32_t bits = (st.x - cen.x >= 0.0f ? 1u : 0u) | (st.z - cen.z >= 0.0f ? 2u : 0u) |
                   (st.y - cen.y >= 0.0f ? 4u : 0u);
-  sm.w(sm.fslot(mesh, sp, 0)) = w.cur;
-  sm.w(sm.fslot(mesh, sp, 1)) = bits;
-  sm.f(sm.fslot(mesh, sp, 2)) = split_param(st.x, r.dir.x, cen.x);
-  sm.f(sm.fslot(mesh, sp, 3)) = split_param(st.y, r.dir.y, cen.y);
-  sm.f(sm.fslot(mesh, sp, 4)) = split_param(st.z, r.dir.z, cen.z);
-  sm.f(sm.fslot(mesh, sp, 5)) = st.x;
-  sm.f(sm.fslot(mesh, sp, 6)) = st.y;
-  sm.f(sm.fslot(mesh, sp, 7)) = st.z;
+  if (inside) bits |= 64u;
+  sm.w(sm.fslot(mesh, sp, 0)) = w.cur | (bits << FS2_PH_NODE_BITS);
+  sm.f(sm.fslot(mesh, sp, 1)) = split_param(st.x, r.dir.x, cen.x);
+  sm.f(sm.fslot(mesh, sp, 2)) = split_param(st.y, r.dir.y, cen.y);
+  sm.f(sm.fslot(mesh, sp, 3)) = split_param(st.z, r.dir.z, cen.z);
+  sm.f(sm.fslot(mesh, sp, 4)) = nparam;  // st is rebuilt from it (outside origins only)
   sp++;
-  w.cur = n.first + bits;
+  w.cur = n.first + (bits & 7u);
   prefetch_l1(S.nodes + 2 * (size_t)w.cur);
   // stays in PH_ENTER
 }
@@ -226,8 +230,9 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
     return;
   }
   const int f = sp - 1;
-  uint32_t node = sm.w(sm.fslot(mesh, f, 0));
-  uint32_t bits = sm.w(sm.fslot(mesh, f, 1));
+  const uint32_t packed = sm.w(sm.fslot(mesh, f, 0));
+  const uint32_t node = packed & ((1u << FS2_PH_NODE_BITS) - 1u);
+  uint32_t bits = packed >> FS2_PH_NODE_BITS;
   NodeRec pn = load_node(S, node);
   if (ret) {
     bits |= 32u;
@@ -237,8 +242,8 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
       return;
     }
   }
-  float tx = sm.f(sm.fslot(mesh, f, 2)), ty = sm.f(sm.fslot(mesh, f, 3)),
-        tz = sm.f(sm.fslot(mesh, f, 4));
+  float tx = sm.f(sm.fslot(mesh, f, 1)), ty = sm.f(sm.fslot(mesh, f, 2)),
+        tz = sm.f(sm.fslot(mesh, f, 3));
   uint32_t visits = ((bits >> 3) & 3u) + 1u;
   bool x_hit = tx <= 1.0f, y_hit = ty <= 1.0f, z_hit = tz <= 1.0f;
   float t = 0.f;
@@ -246,20 +251,23 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
   int consumed = 0;
   if (x_hit && tx < ty && tx < tz) {
     t = tx;
-    consumed = 2;
+    consumed = 1;
     flip = 1u;
   } else if (y_hit && ty < tz && ty < tx) {
     t = ty;
-    consumed = 3;
+    consumed = 2;
     flip = 4u;
   } else if (z_hit && tz < ty && tz < tx) {
     t = tz;
-    consumed = 4;
+    consumed = 3;
     flip = 2u;
   }
   bool go = flip != 0u && visits < 4u;
   if (go) {
-    V3 st = v3(sm.f(sm.fslot(mesh, f, 5)), sm.f(sm.fslot(mesh, f, 6)), sm.f(sm.fslot(mesh, f, 7)));
+    // the point the node was entered at: the origin, or ray_box's entry point, rebuilt with
+    // ray_box's own expression (start + (stop - start) * param)
+    V3 st = r.start;
+    if (!(bits & 64u)) st = r.start + (r.stop - r.start) * sm.f(sm.fslot(mesh, f, 4));
     go = point_in_box(pn.mn, pn.mx, st + r.dir * t);
   }
   if (!go) {
@@ -269,7 +277,7 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
   }
   sm.f(sm.fslot(mesh, f, consumed)) = FS2_INFINITY;
   bits = ((bits ^ flip) & ~(3u << 3)) | (visits << 3);
-  sm.w(sm.fslot(mesh, f, 1)) = bits;
+  sm.w(sm.fslot(mesh, f, 0)) = node | (bits << FS2_PH_NODE_BITS);
   w.cur = pn.first + (bits & 7u);
   prefetch_l1(S.nodes + 2 * (size_t)w.cur);
   w.st = PH_ENTER;

@@ -192,7 +192,7 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #define FS2_WF_COOP_TRIS 1  // triangle groups tested by 4 lanes each (ph_lb_tris_coop)
 #endif
 #ifndef FS2_WF_MIN_BLOCKS
-#define FS2_WF_MIN_BLOCKS 6  // measured (no scene tree, Mpaths/s): 5 -> 400 (92 regs), 6 -> 433 (80 regs, 12 B spilled), 7 -> 434, 8 -> 398
+#define FS2_WF_MIN_BLOCKS 7  // measured (no scene tree, Mpaths/s): r1_h 5 -> 400, 6 -> 433, 7 -> 434, 8 -> 398; with 152 B/lane stacks 6 -> 472, 7 -> 479 (72 regs)
 #endif
 // TREE = false: the scene has no scene octree (< 182 objects), which lets the
 // compiler drop the scene-leaf bookkeeping (second hit record, leaf cursor) from the loop.

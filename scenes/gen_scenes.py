@@ -362,6 +362,59 @@ def scene_grid(outdir, nx, nz, name, aperture=1.5):
     return s
 
 
+def scene_random(outdir, seed):
+    """Seeded random scene for the fuzz parity test: random camera (inside the cloud for odd
+    seeds), spheres / rotated cuboids / tilted quads of every material, one or two small
+    meshes at random transforms, and for every fourth seed enough objects to switch the scene
+    octree on."""
+    rng = np.random.RandomState(1000 + seed)
+    s = "# fs2-b200 random scene %d\n" % seed
+    s += common_materials(outdir, textured_floor=bool(seed & 1))
+    s += block("sky", material="sky_mat")
+    far = seed % 2 == 0
+    pos = (rng.uniform(-30, 30), rng.uniform(4, 30), rng.uniform(-70, -40)) if far else \
+          (rng.uniform(-10, 10), rng.uniform(3, 15), rng.uniform(-10, 10))
+    s += camera(position=pos, target=(rng.uniform(-5, 5), rng.uniform(2, 10), rng.uniform(-5, 5)),
+                fov=rng.uniform(30, 70), aperture=0.0)
+    mats = ["red_diffuse", "green_ceramic", "gold_metal", "mirror_mat", "glass_mat", "frost_mat",
+            "liquid_mat", "blue_cuboid", "floor_mat", "lamp_mat"]
+    s += block("quad", material="floor_mat", position=(0, 0, 0),
+               normal=(rng.uniform(-0.1, 0.1), 1.0, rng.uniform(-0.1, 0.1)), width=150.0, height=150.0)
+    n = int(rng.randint(6, 30)) if seed % 4 else int(rng.randint(190, 260))
+    for k in range(n):
+        p3 = (rng.uniform(-35, 35), rng.uniform(0.5, 24.0), rng.uniform(-35, 35))
+        m = mats[int(rng.randint(len(mats)))]
+        kind = rng.randint(10)
+        if kind < 6:
+            s += block("sphere", material=m, position=p3, radius=rng.uniform(0.5, 5.0))
+        elif kind < 9:
+            s += block("cuboid", material=m, position=p3, width=rng.uniform(1, 8),
+                       height=rng.uniform(1, 8), depth=rng.uniform(1, 8),
+                       rotation=(rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(-1, 1),
+                                 rng.uniform(0, 3)))
+        else:
+            s += block("quad", material=m, position=p3,
+                       normal=(rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(-1, 1)),
+                       width=rng.uniform(2, 20), height=rng.uniform(2, 20))
+    for k in range(1 + seed % 2):
+        if (seed + k) % 3 == 0:
+            obj = os.path.join(outdir, "rnd_knot_%d.obj" % (seed % 3))
+            if not os.path.exists(obj):
+                torus_knot_obj(obj, 48 + 16 * (seed % 3), 8)
+        else:
+            nu = 16 + 8 * ((seed + k) % 4)
+            obj = os.path.join(outdir, "rnd_sphere_%d.obj" % nu)
+            if not os.path.exists(obj):
+                uv_sphere_obj(obj, nu, nu // 2 + 1)
+        sc = rng.uniform(2, 7)
+        s += block("mesh", file=obj, material=mats[int(rng.randint(8))],
+                   translation=(rng.uniform(-15, 15), rng.uniform(4, 14), rng.uniform(-15, 15)),
+                   scale=(sc, sc * rng.uniform(0.6, 1.4), sc),
+                   rotation=(rng.uniform(-1, 1), rng.uniform(-1, 1), rng.uniform(-1, 1),
+                             rng.uniform(0, 3)))
+    return s
+
+
 SCENES = {
     "demo": lambda d: scene_demo(d),
     "demo_dof": lambda d: scene_demo(d, aperture=1.5),
@@ -385,7 +438,7 @@ def generate(outdir, names=None):
     for n in (names or SCENES.keys()):
         p = os.path.join(outdir, n + ".scene")
         if not os.path.exists(p):
-            text = SCENES[n](outdir)
+            text = scene_random(outdir, int(n[6:])) if n.startswith("random") else SCENES[n](outdir)
             with open(p + ".tmp", "w") as f:
                 f.write(text)
             os.replace(p + ".tmp", p)
