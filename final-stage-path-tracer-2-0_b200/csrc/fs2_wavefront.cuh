@@ -176,6 +176,9 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #ifndef FS2_WF_REP_OBJ
 #define FS2_WF_REP_OBJ 3
 #endif
+#ifndef FS2_WF_REP_OBJ_TREE
+#define FS2_WF_REP_OBJ_TREE 16
+#endif
 #ifndef FS2_WF_REP_ENTER
 #define FS2_WF_REP_ENTER 3
 #endif
@@ -264,7 +267,9 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
         break;
       }
     }
-    FS2_PHASE_N(PH_OBJ, FS2_WF_REP_OBJ, FS2_WF_REPEAT_MIN, (ph_object<STATS, TREE>(S, w, ray, c)))
+    // scene-tree leaves hold tens of objects (the reference's tree is shallow): stay in the phase
+    FS2_PHASE_N(PH_OBJ, (TREE ? FS2_WF_REP_OBJ_TREE : FS2_WF_REP_OBJ), FS2_WF_REPEAT_MIN,
+                (ph_object<STATS, TREE>(S, w, ray, c)))
     FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, (ph_enter<STATS, TREE>(S, w, ray, sm, c)))
     FS2_PHASE_N(PH_LB_NODE, FS2_WF_REP_NODE, FS2_WF_REPEAT_MIN, ph_lb_node<STATS>(S, w, ray, q, sm, c))
 #if FS2_WF_COOP_TRIS
