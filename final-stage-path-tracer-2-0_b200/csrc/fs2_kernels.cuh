@@ -348,8 +348,7 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
   w.flags = 0;
   w.lb_cur = w.lb_root = 0;
   w.lb_sp = 0;
-  w.bt = w.bu = w.bv = 0.f;
-  w.border = w.qbase = w.qcount = w.qmask = 0;
+  w.qbase = w.qcount = w.qmask = 0;
   LbRay q = make_lbray(ps.ray);
   if (mine) {
     begin_path(cam, tp, pixel, px, py, ps);

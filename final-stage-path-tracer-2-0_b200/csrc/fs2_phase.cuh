@@ -74,8 +74,6 @@ struct PhLane {
   // leaf BVH walk
   uint32_t lb_cur, lb_root;
   int lb_sp;
-  float bt, bu, bv;
-  uint32_t border;
   uint32_t qbase, qcount, qmask;  // pending triangle groups of the current node; bit31 of qcount: found
 };
 
@@ -163,9 +161,8 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
         w.st = PH_RETURN;
       } else {
         if (STATS) c.n_tri += n.count;
-        w.bt = w.rec.param;
-        w.bu = w.bv = 0.f;
-        w.border = 0;
+        // the leaf's running best lives in w.rec itself: a record of this leaf overwrites it
+        // only when it is accepted; PH_F_FOUND says that it holds one (rec.prim = its leaf rank)
         w.flags &= ~PH_F_FOUND;
         w.lb_sp = 0;
         w.lb_root = root;
@@ -331,12 +328,7 @@ __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray&
 // Leaf finished: publish the best of this leaf and return to the octree walk.
 __device__ __forceinline__ void ph_leaf_done(PhLane& w) {
   if (w.flags & PH_F_FOUND) {
-    w.rec.param = w.bt;
-    w.rec.object = w.cur_obj;
-    w.rec.prim = w.border;
-    w.rec.u = w.bu;
-    w.rec.v = w.bv;
-    w.flags |= PH_F_RET;
+    w.flags |= PH_F_RET;  // w.rec already is the leaf's best
   } else {
     w.flags &= ~PH_F_RET;
   }
@@ -348,7 +340,7 @@ __device__ __forceinline__ void ph_lb_pop(PhLane& w, const DScene& S, const PhSm
   while (w.lb_sp > 0) {
     --w.lb_sp;
     uint32_t e = sm.w(sm.lslot(w.lb_sp));
-    if (__uint_as_float(e << 16) <= fminf(w.bt, 1.0f)) {
+    if (__uint_as_float(e << 16) <= fminf(w.rec.param, 1.0f)) {
       w.lb_cur = w.lb_root + (e >> 16);
       prefetch_l1(S.lb_nodes + 8 * (size_t)w.lb_cur);
       w.st = PH_LB_NODE;
@@ -367,7 +359,7 @@ __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray
   uint4 meta = __ldg((const uint4*)(nd + 6));
   if (STATS) c.n_lbnode++;
   const V3 s = r.start;
-  float lim = fminf(w.bt, 1.0f);
+  float lim = fminf(w.rec.param, 1.0f);
   float t0 = lb_child(lx.x, ly.x, lz.x, hx.x, hy.x, hz.x, s, q, lim);
   float t1 = lb_child(lx.y, ly.y, lz.y, hx.y, hy.y, hz.y, s, q, lim);
   float t2 = lb_child(lx.z, ly.z, lz.z, hx.z, hy.z, hz.z, s, q, lim);
@@ -430,9 +422,12 @@ __device__ __forceinline__ void ph_lb_tris(const DScene& S, PhLane& w, const Ray
   uint32_t rem = w.qcount - 4u * g;
   bool found = (w.flags & PH_F_FOUND) != 0;
   if (w.qmask) prefetch_l1(S.lb_plane + w.qbase + 4u * ((uint32_t)__ffs((int)w.qmask) - 1u));
-  lb_test_group<STATS>(S, w.qbase + 4u * g, rem < 4u ? rem : 4u, r.start, r.dir, w.bt, w.border,
-                       found, w.bu, w.bv, c);
-  if (found) w.flags |= PH_F_FOUND;
+  lb_test_group<STATS>(S, w.qbase + 4u * g, rem < 4u ? rem : 4u, r.start, r.dir, w.rec.param,
+                       w.rec.prim, found, w.rec.u, w.rec.v, c);
+  if (found) {
+    w.rec.object = w.cur_obj;
+    w.flags |= PH_F_FOUND;
+  }
   if (!w.qmask) ph_lb_pop(w, S, sm);
 }
 
@@ -481,8 +476,8 @@ __device__ __forceinline__ void ph_lb_tris_coop(const DScene& S, PhLane& w, cons
                     __shfl_sync(FULL, r.start.z, src));
     const V3 d = v3(__shfl_sync(FULL, r.dir.x, src), __shfl_sync(FULL, r.dir.y, src),
                     __shfl_sync(FULL, r.dir.z, src));
-    const float bt = __shfl_sync(FULL, w.bt, src);
-    const uint32_t border = __shfl_sync(FULL, w.border, src);
+    const float bt = __shfl_sync(FULL, w.rec.param, src);
+    const uint32_t border = __shfl_sync(FULL, w.rec.prim, src);
     const bool found = __shfl_sync(FULL, w.flags & PH_F_FOUND, src) != 0u;
     float kt = FS2_INFINITY, u = 0.f, v = 0.f;
     uint32_t kord = 0xFFFFFFFFu;
@@ -526,10 +521,11 @@ __device__ __forceinline__ void ph_lb_tris_coop(const DScene& S, PhLane& w, cons
     const uint32_t ro = __shfl_sync(FULL, kord, from);
     const float ru = __shfl_sync(FULL, u, from), rv = __shfl_sync(FULL, v, from);
     if (served && ro != 0xFFFFFFFFu) {
-      w.bt = rt;
-      w.border = ro;
-      w.bu = ru;
-      w.bv = rv;
+      w.rec.param = rt;
+      w.rec.object = w.cur_obj;
+      w.rec.prim = ro;
+      w.rec.u = ru;
+      w.rec.v = rv;
       w.flags |= PH_F_FOUND;
     }
     const unsigned served_mask = __ballot_sync(FULL, served);

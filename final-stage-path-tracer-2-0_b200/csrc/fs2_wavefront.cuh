@@ -195,7 +195,7 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #define FS2_WF_COOP_TRIS 1  // triangle groups tested by 4 lanes each (ph_lb_tris_coop)
 #endif
 #ifndef FS2_WF_MIN_BLOCKS
-#define FS2_WF_MIN_BLOCKS 7  // measured (no scene tree, Mpaths/s): r1_h 5 -> 400, 6 -> 433, 7 -> 434, 8 -> 398; with 152 B/lane stacks 6 -> 472, 7 -> 479 (72 regs)
+#define FS2_WF_MIN_BLOCKS 8  // measured (no scene tree, Mpaths/s): r1_h 5 -> 400, 6 -> 433, 7 -> 434, 8 -> 398; r1_k (152 B/lane stacks) 6 -> 472, 7 -> 479; r1_l (leaf best kept in the record) 6 -> 491, 7 -> 504, 8 -> 521 (64 regs)
 #endif
 // TREE = false: the scene has no scene octree (< 182 objects), which lets the
 // compiler drop the scene-leaf bookkeeping (second hit record, leaf cursor) from the loop.
@@ -226,8 +226,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   w.flags = 0;
   w.lb_cur = w.lb_root = 0;
   w.lb_sp = 0;
-  w.bt = w.bu = w.bv = 0.f;
-  w.border = w.qbase = w.qcount = w.qmask = 0;
+  w.qbase = w.qcount = w.qmask = 0;
   uint32_t chunk_next = 0, chunk_end = 0;
   bool exhausted = false;
   const uint32_t fetch_min = max(1u, tp.tune & 31u);
