@@ -169,11 +169,11 @@ KERNEL_NAME = ["k_trace_phase<0>"]
 # --------------------------------------------------------------------------- roofline
 # DRAM bytes of one launch of each wavefront kernel on a full 4 194 304-path wave of the bench
 # scene: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture each
-# (profiles/r1_h_wf_trace_ncu_full_details.txt: 279.2 + 53.2 MB; r1_h_wf_shade_...: 526.6 + 321.3 MB;
-# unchanged in r1_j: 280.3 + 52.6 and 526.7 + 322.2 MB).
+# (first measured in profiles/r1_h_*: 279.2 + 53.2 MB and 526.6 + 321.3 MB; current numbers from
+# r1_l: 295.5 + 60.2 and 526.5 + 322.7 MB).
 # Per ray segment that is 281 B, against the ~212 B of path state + hit record the pipeline moves
 # by design; the scene itself is served from L2.
-PROFILED_DRAM_BYTES_PER_SEGMENT = (279.206656e6 + 53.182208e6 + 526.639360e6 + 321.259008e6) / 4194304.0
+PROFILED_DRAM_BYTES_PER_SEGMENT = (295.546368e6 + 60.236032e6 + 526.524672e6 + 322.659072e6) / 4194304.0
 
 
 def roofline(ctx_stats, objects, n_pixels, kernel_ms, peaks):
@@ -376,7 +376,7 @@ def run_gpu(args, rank, world, local_rank):
         if args.variant == "wavefront":
             roof["traffic"] = PROFILED_DRAM_BYTES_PER_SEGMENT * sst["n_segments"]
             roof["traffic_source"] = ("ncu --set full, one k_wf_trace + one k_wf_shade launch on a full "
-                                      "wave (profiles/r1_h_*), scaled by this run's ray segments")
+                                      "wave (profiles/r1_l_*), scaled by this run's ray segments")
         try:
             cpu = cpu_sample(scene_file) if (world == 1 and not args.skip_cpu) else None
         except Exception as e:  # the reference binary did not travel
