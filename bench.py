@@ -171,7 +171,7 @@ KERNEL_NAME = ["k_trace_phase<0>"]
 # scene: dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture each
 # (first measured in profiles/r1_h_*: 279.2 + 53.2 MB and 526.6 + 321.3 MB; current numbers from
 # r1_l: 295.5 + 60.2 and 526.5 + 322.7 MB).
-# Per ray segment that is 281 B, against the ~212 B of path state + hit record the pipeline moves
+# Per ray segment that is 287 B, against the ~212 B of path state + hit record the pipeline moves
 # by design; the scene itself is served from L2.
 PROFILED_DRAM_BYTES_PER_SEGMENT = (295.546368e6 + 60.236032e6 + 526.524672e6 + 322.659072e6) / 4194304.0
 
