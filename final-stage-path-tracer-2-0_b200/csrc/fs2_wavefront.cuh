@@ -37,7 +37,8 @@ namespace fs2 {
 
 #define FS2_WF_PLANES 6          // float4 planes of per-path state
 #define FS2_WF_CHUNK 128         // most ray indices a warp reserves per atomic
-#define FS2_WF_MAX_PATHS (1u << 23)  // pool size bound (state: 2 x 96 B + 20 B per path = 1.8 GB)
+#define FS2_WF_MAX_PATHS (1u << 25)  // pool size bound (state: 2 x 96 B + 20 B per path = 7.1 GB); measured on
+                                     // config 2 at r1_l: 4 M -> 492, 8 M -> 520, 16 M -> 537, 32 M -> 544, 64 M -> 543 Mpaths/s
 
 // counters (uint32): 0 continuing paths of this wave, 1 continuing paths of the next wave,
 //                    2 fetch cursor of k_wf_trace, 3 current state array, 6 waves run,
