@@ -72,6 +72,22 @@ class fs_mesh_tree(C.Structure):
                 ("n_nodes", C.c_uint32), ("n_tris", C.c_uint32), ("build_ms", C.c_float)]
 
 
+class fs_post_params(C.Structure):
+    _fields_ = [("denoise_passes", C.c_int32), ("sigma_normal", C.c_float),
+                ("sigma_depth", C.c_float), ("sigma_colour", C.c_float),
+                ("bloom_threshold", C.c_float), ("bloom_strength", C.c_float),
+                ("bloom_radius", C.c_int32), ("flare_strength", C.c_float),
+                ("flare_ghosts", C.c_int32)]
+
+
+def post_params(denoise_passes=4, sigma_normal=64.0, sigma_depth=0.02, sigma_colour=4.0,
+                bloom_threshold=1.0, bloom_strength=0.0, bloom_radius=12, flare_strength=0.0,
+                flare_ghosts=0):
+    return fs_post_params(denoise_passes, sigma_normal, sigma_depth, sigma_colour,
+                          bloom_threshold, bloom_strength, bloom_radius, flare_strength,
+                          flare_ghosts)
+
+
 class fs_stats(C.Structure):
     _fields_ = [("n_paths", C.c_uint64), ("n_segments", C.c_uint64), ("n_node", C.c_uint64),
                 ("n_tri", C.c_uint64), ("n_bary", C.c_uint64), ("n_prim", C.c_uint64),

@@ -4,6 +4,8 @@
 // source/main.cpp:61-76) plus --spp, --seed, --device, --out, --focus x,y (the click-to-focus
 // of source/main.cpp:144-153 through TraceRange), --fast (Camera::fast_render_enabled) and
 // --checkpoint / --resume (the accumulation film on disk: a render continues where it stopped).
+// --post-out image.ppm writes the film after the device post-processing chain (--denoise passes,
+// --bloom strength[,threshold[,radius]], --flare strength[,ghosts]).
 // Written against the mirrored API of host/fs2_host.h only.
 //
 //   fs2_render -f scene.scene -w 1920 -h 1080 --spp 64 --out image.ppm [--pfm mean.pfm]
@@ -13,6 +15,7 @@
 #include <string.h>
 
 #include <string>
+#include <vector>
 
 #include "fs2_host.h"
 
@@ -28,6 +31,14 @@ static bool write_ppm(const std::string& path, DisplayFrame* f) {
     fwrite(rgb + 3 * (size_t)(h - 1 - y) * w, 1, 3 * (size_t)w, fp);
   fclose(fp);
   return true;
+}
+
+static bool write_ppm_bytes(const std::string& path, const uint8* rgb, uint32 w, uint32 h) {
+  FILE* fp = fopen(path.c_str(), "wb");
+  if (!fp) return false;
+  fprintf(fp, "P6\n%u %u\n255\n", w, h);
+  for (uint32 y = 0; y < h; y++) fwrite(rgb + 3 * (size_t)(h - 1 - y) * w, 1, 3 * (size_t)w, fp);
+  return fclose(fp) == 0;
 }
 
 static bool write_pfm(const std::string& path, DisplayFrame* f) {
@@ -46,6 +57,8 @@ int main(int argc, char** argv) {
   uint64 seed = 1;
   int device = 0;
   bool fast = false, have_focus = false;
+  PostProcess post;
+  std::string post_out;
   float fx = 0, fy = 0;
   for (int i = 1; i < argc; i++) {
     const char* a = argv[i];
@@ -58,6 +71,14 @@ int main(int argc, char** argv) {
     else if (!strcmp(a, "--fast")) fast = true;
     else if (!strcmp(a, "--checkpoint")) checkpoint = next();
     else if (!strcmp(a, "--resume")) resume = next();
+    else if (!strcmp(a, "--post-out")) post_out = next();
+    else if (!strcmp(a, "--denoise")) post.denoise_passes = atoi(next());
+    else if (!strcmp(a, "--bloom"))  // strength[,threshold[,radius]]
+      sscanf(next(), "%f,%f,%d", &post.bloom_strength, &post.bloom_threshold, &post.bloom_radius);
+    else if (!strcmp(a, "--flare")) {  // strength[,ghosts]
+      post.flare_ghosts = 3;
+      sscanf(next(), "%f,%d", &post.flare_strength, &post.flare_ghosts);
+    }
     else if (!strcmp(a, "--focus")) have_focus = sscanf(next(), "%f,%f", &fx, &fy) == 2;
     else if (a[0] == '-' && (a[1] == 'f' || (a[1] == '-' && a[2] == 'f'))) file = next();
     else if (a[0] == '-' && (a[1] == 'w' || (a[1] == '-' && a[2] == 'w'))) width = (uint32)atoi(next());
@@ -70,7 +91,9 @@ int main(int argc, char** argv) {
   if (file.empty()) {  // source/main.cpp:78-81
     fprintf(stderr, "usage: fs2_render -f <scene file> [-w W] [-h H] [--spp N] [--seed S] "
                     "[--device D] [--out image.ppm] [--pfm mean.pfm] [--focus x,y] [--fast] "
-                    "[--resume film.ckpt] [--checkpoint film.ckpt]\n");
+                    "[--resume film.ckpt] [--checkpoint film.ckpt] [--post-out image.ppm "
+                    "[--denoise passes] [--bloom strength[,threshold[,radius]]] "
+                    "[--flare strength[,ghosts]]]\n");
     return 2;
   }
   Scene scene;
@@ -107,6 +130,17 @@ int main(int argc, char** argv) {
   if (!write_ppm(out, &frame)) {
     fprintf(stderr, "cannot write %s\n", out.c_str());
     return 1;
+  }
+  if (!post_out.empty()) {  // denoise / bloom / flare of the finished film, on the device
+    std::vector<uint8> bytes(3 * (size_t)width * height);
+    if (!PostProcessFrame(&frame, post, nullptr, bytes.data())) {
+      fprintf(stderr, "post-processing failed: %s\n", LastTraceError());
+      return 1;
+    }
+    if (!write_ppm_bytes(post_out, bytes.data(), width, height)) {
+      fprintf(stderr, "cannot write %s\n", post_out.c_str());
+      return 1;
+    }
   }
   if (!pfm.empty() && !write_pfm(pfm, &frame)) {
     fprintf(stderr, "cannot write %s\n", pfm.c_str());

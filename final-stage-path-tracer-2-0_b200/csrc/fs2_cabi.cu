@@ -20,6 +20,7 @@
 
 #include "fs2_kernels.cuh"
 #include "fs2_build.cuh"
+#include "fs2_post.cuh"
 #include "fs2_lbvh_build.h"
 
 using namespace fs2;
@@ -53,7 +54,7 @@ struct fs_ctx {
   uint32_t n_nodes = 0, n_tris = 0, n_faces = 0, n_materials = 0;
   // film
   int width = 0, height = 0;
-  DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch, auxpack;
+  DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch, auxpack, post;
   DeviceBuf wf_planes, wf_hit, wf_counters;  // wavefront path state
   uint32_t* wf_host_live = nullptr;   // pinned: live paths of the newest wave, per pipe
   cudaEvent_t wf_events[FS2_WF_AHEAD * FS2_WF_PIPES] = {};
@@ -425,7 +426,7 @@ int fs_destroy(fs_ctx* ctx) {
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
                       &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
-                      &ctx->scratch, &ctx->auxpack, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters};
+                      &ctx->scratch, &ctx->auxpack, &ctx->post, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters};
   for (DeviceBuf* b : all) dev_free(b);
   if (ctx->d_stats) cudaFree(ctx->d_stats);
   if (ctx->wf_host_live) {
@@ -700,6 +701,66 @@ int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8, f
     if (mat_id) CUDA_TRY(ctx, cudaMemcpyAsync(mat_id, d_ids, n * 8, cudaMemcpyDeviceToHost, ctx->stream));
   }
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_film_post(fs_ctx* ctx, const fs_post_params* pr, float* rgb, uint8_t* rgb8) {
+  if (!ctx || !pr) return fail(ctx, FS_E_INVALID, "fs_film_post: null argument");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_post before fs_film_resize");
+  if (pr->denoise_passes < 0 || pr->denoise_passes > 8 || pr->flare_ghosts < 0 ||
+      pr->flare_ghosts > 16)
+    return fail(ctx, FS_E_INVALID, "fs_film_post: denoise_passes in 0..8, flare_ghosts in 0..16");
+  const bool glow = pr->bloom_strength > 0.0f || (pr->flare_strength > 0.0f && pr->flare_ghosts > 0);
+  if (glow && (pr->bloom_radius < 1 || pr->bloom_radius > 128))
+    return fail(ctx, FS_E_INVALID, "fs_film_post: bloom_radius in 1..128");
+  if (pr->denoise_passes && !(pr->sigma_depth > 0.0f && pr->sigma_colour >= 0.0f && pr->sigma_normal >= 0.0f))
+    return fail(ctx, FS_E_INVALID, "fs_film_post: sigma_depth > 0, sigma_colour >= 0, sigma_normal >= 0");
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  const int w = ctx->width, h = ctx->height, n = w * h;
+  // planes: A, B, C (float4 each), sigma (float), out rgb (3 floats), out rgb8 (3 bytes)
+  if ((rc = dev_alloc(ctx, &ctx->post, (size_t)n * (48 + 4 + 12 + 3) + 64))) return rc;
+  float4* A = (float4*)ctx->post.p;
+  float4 *B = A + n, *C = B + n;
+  float* sigma = (float*)(C + n);
+  float* d_rgb = sigma + n;
+  uint8_t* d_rgb8 = (uint8_t*)(d_rgb + 3 * (size_t)n);
+  const float4* aux = (const float4*)ctx->aux.p;
+  const uint32_t* ids = (const uint32_t*)ctx->mat_id.p;
+  PostParams pp{pr->sigma_normal, pr->sigma_depth, pr->sigma_colour, pr->bloom_threshold,
+                pr->bloom_strength, pr->bloom_radius, pr->flare_strength, pr->flare_ghosts};
+  const dim3 g2((w + 31) / 32, (h + 7) / 8);
+  const int g1 = (n + 255) / 256;
+  cudaStream_t st = ctx->stream;
+  k_post_prep<<<g1, 256, 0, st>>>((const float*)ctx->mean.p, n, A);
+  ctx->launches++;
+  float4 *cur = A, *other = B;
+  if (pr->denoise_passes) {
+    k_post_sigma<<<g2, 256, 0, st>>>(cur, ids, w, h, sigma);
+    ctx->launches++;
+    float scale = 1.0f;
+    for (int i = 0; i < pr->denoise_passes; i++, scale *= 0.5f) {
+      k_post_atrous<<<g2, 256, 0, st>>>(cur, aux, ids, sigma, w, h, 1 << i, scale, pp, other);
+      ctx->launches++;
+      float4* t = cur;
+      cur = other;
+      other = t;
+    }
+  }
+  const float4* glow_plane = nullptr;
+  if (glow) {
+    k_post_bright<<<g1, 256, 0, st>>>(cur, n, pr->bloom_threshold, other);
+    k_post_blur<<<g2, 256, 0, st>>>(other, w, h, pr->bloom_radius, 0, C);
+    k_post_blur<<<g2, 256, 0, st>>>(C, w, h, pr->bloom_radius, 1, other);
+    ctx->launches += 3;
+    glow_plane = other;
+  }
+  k_post_compose<<<g2, 256, 0, st>>>(cur, glow_plane, w, h, pp, d_rgb, d_rgb8);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  if (rgb) CUDA_TRY(ctx, cudaMemcpyAsync(rgb, d_rgb, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
+  if (rgb8) CUDA_TRY(ctx, cudaMemcpyAsync(rgb8, d_rgb8, (size_t)n * 3, cudaMemcpyDeviceToHost, st));
+  CUDA_TRY(ctx, cudaStreamSynchronize(st));
   return FS_OK;
 }
 

@@ -11,6 +11,7 @@ _SYMBOLS = {
     "fs_abi_version": (C.c_int, []),
     "fs_film_save": (C.c_int, [C.c_void_p, C.c_void_p]),
     "fs_film_load": (C.c_int, [C.c_void_p, C.c_void_p]),
+    "fs_film_post": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_post_params), C.c_void_p, C.c_void_p]),
     "fs_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
     "fs_host_unregister": (C.c_int, [C.c_void_p]),
     "fs_mesh_tree_build": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,
@@ -177,6 +178,19 @@ class Context:
                                           _ptr(film.get("normal")), _ptr(film.get("depth")),
                                           _ptr(film.get("mat_id"))))
         return film
+
+    def post_film(self, params, rgb=True, rgb8=True):
+        """Denoise / bloom / flare of the resolved film on the device (fs_film_post);
+        params = abi.post_params(...).  The film itself is left as it is."""
+        n = self.width * self.height
+        out = {}
+        if rgb:
+            out["rgb"] = np.empty((n, 3), np.float32)
+        if rgb8:
+            out["rgb8"] = np.empty((n, 3), np.uint8)
+        self._check(self.lib.fs_film_post(self.handle, C.byref(params), _ptr(out.get("rgb")),
+                                          _ptr(out.get("rgb8"))))
+        return out
 
     def save_film(self):
         """Accumulation film (rgb sum, count per pixel) as a numpy array: a checkpoint."""

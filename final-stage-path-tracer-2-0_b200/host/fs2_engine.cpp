@@ -190,6 +190,22 @@ struct CheckpointHeader {
 };
 }  // namespace
 
+bool PostProcessFrame(DisplayFrame* frame, const PostProcess& post, float* rgb, uint8* rgb8) {
+  TraceState& st = state();
+  if (!frame || !st.ctx || st.frame != frame->impl() || frame->impl()->device_dirty) {
+    fail_msg("PostProcessFrame: the frame has no samples on the device");
+    return false;
+  }
+  fs_post_params p = {post.denoise_passes, post.sigma_normal, post.sigma_depth, post.sigma_colour,
+                      post.bloom_threshold, post.bloom_strength, post.bloom_radius,
+                      post.flare_strength, post.flare_ghosts};
+  if (fs_film_post(st.ctx, &p, rgb, rgb8) != FS_OK) {
+    fail("fs_film_post", st.ctx);
+    return false;
+  }
+  return true;
+}
+
 bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path) {
   TraceState& st = state();
   if (!frame || !path || !st.ctx || st.frame != frame->impl() || frame->impl()->device_dirty) {

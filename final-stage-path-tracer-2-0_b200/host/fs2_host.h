@@ -268,5 +268,19 @@ const char* LastTraceError();
 bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path);
 bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path);
 
+// Film post-processing on the device (fs_film_post): guided a-trous denoise, bloom and flare of
+// the frame's resolved image, using its normal / depth / material-id planes (frame.h:86-91).
+// The reference's README describes these stages, its code has none.  Outputs (either may be
+// null): rgb = 3 floats per pixel, rgb8 = display bytes; the frame itself is not modified.
+struct PostProcess {
+  int denoise_passes = 0;
+  float sigma_normal = 64.0f, sigma_depth = 0.02f, sigma_colour = 4.0f;
+  float bloom_threshold = 1.0f, bloom_strength = 0.0f;
+  int bloom_radius = 12;
+  float flare_strength = 0.0f;
+  int flare_ghosts = 0;
+};
+bool PostProcessFrame(DisplayFrame* frame, const PostProcess& post, float* rgb, uint8* rgb8);
+
 }  // namespace base
 #endif

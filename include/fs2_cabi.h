@@ -280,6 +280,34 @@ int fs_film_save(fs_ctx* ctx, float* sum_rgba);
 int fs_film_load(fs_ctx* ctx, const float* sum_rgba);
 int fs_film_resolve(fs_ctx* ctx);
 
+/*
+ * Film post-processing on the device.  The reference's README describes
+ * variance-adaptive denoising, bloom and flare; its code implements none of them but keeps the
+ * guide buffers for it (normal / depth / material id, reference source/frame.h:86-91).  This
+ * call filters the resolved mean image with those guides; the film itself is not modified, so
+ * accumulation can continue.  Stages (each off when its count / strength is 0):
+ *   denoise : `denoise_passes` edge-avoiding a-trous passes (stride 1, 2, 4, ...), weights from
+ *             normal^sigma_normal, relative depth / sigma_depth, luminance difference in units of
+ *             sigma_colour local standard deviations; taps of another material id are rejected
+ *   bloom   : luminance above bloom_threshold, Gaussian of bloom_radius pixels, x bloom_strength
+ *   flare   : flare_ghosts mirrored copies of the blurred bright pass through the image centre
+ * Multi-ray anti-aliasing (k jittered rays per pixel per call) is fs_trace's n_samples.
+ * Outputs are host arrays (either may be NULL): rgb = 3 floats / pixel, rgb8 = display bytes
+ * with DisplayFrame's gamma (frame.cpp:60-69).
+ */
+typedef struct fs_post_params {
+  int32_t denoise_passes; /* 0 = off, at most 8 */
+  float sigma_normal;     /* e.g. 64   */
+  float sigma_depth;      /* e.g. 0.02 */
+  float sigma_colour;     /* e.g. 4    */
+  float bloom_threshold;  /* e.g. 1.0  */
+  float bloom_strength;   /* 0 = off   */
+  int32_t bloom_radius;   /* pixels, 1..128 */
+  float flare_strength;   /* 0 = off   */
+  int32_t flare_ghosts;   /* 0..16     */
+} fs_post_params;
+int fs_film_post(fs_ctx* ctx, const fs_post_params* params, float* rgb, uint8_t* rgb8);
+
 int fs_get_stats(fs_ctx* ctx, fs_stats* out);
 int fs_reset_stats(fs_ctx* ctx);
 

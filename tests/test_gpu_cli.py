@@ -57,3 +57,29 @@ def test_cli_checkpoint_resume_continues_the_sample_sequence(tmp_path):
     assert np.allclose(whole, resumed, rtol=1e-5, atol=1e-6)
     bad = subprocess.run(common + ["-w", "64", "--spp", "1", "--resume", ck], capture_output=True, text=True)
     assert bad.returncode != 0  # a checkpoint of another frame size is refused
+
+
+def test_cli_post_processing_output(tmp_path):
+    """--post-out: the denoised image is smoother than the raw one at the same samples, bloom
+    only adds light; the raw --out image is unchanged by the post chain."""
+    exe = build.build_cli()
+    scene = gen_scenes.generate(str(tmp_path), ["demo"])["demo"]
+    common = [exe, "-f", scene, "-w", "96", "-h", "64", "--spp", "4", "--seed", "5"]
+
+    def run(extra, name):
+        out, post = str(tmp_path / (name + ".ppm")), str(tmp_path / (name + "_post.ppm"))
+        r = subprocess.run(common + ["--out", out, "--post-out", post] + extra,
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        load = lambda f: np.frombuffer(open(f, "rb").read()[13:], np.uint8).reshape(64, 96, 3).astype(int)
+        return load(out), load(post)
+
+    raw, den = run(["--denoise", "4"], "den")
+    rough = lambda a: np.abs(np.diff(a, axis=1)).mean()
+    assert rough(den) < 0.8 * rough(raw)
+    raw2, glow = run(["--bloom", "0.8,0.5,6", "--flare", "0.3,2"], "glow")
+    assert (raw2 == raw).all()
+    assert (glow >= raw2).all() and (glow > raw2).mean() > 0.05
+    bad = subprocess.run(common + ["--post-out", str(tmp_path / "x.ppm"), "--denoise", "99"],
+                         capture_output=True, text=True)
+    assert bad.returncode != 0 and "post-processing failed" in bad.stderr
