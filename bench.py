@@ -267,6 +267,21 @@ def run_gpu(args, rank, world, local_rank):
             dist.barrier()
         torch.cuda.synchronize()
 
+    # Untimed ramp before the W warm-up steps: at N = 8 a step is ~35 ms, and three of them do not
+    # bring idle GPUs (and NCCL's first reduce) up to steady clocks; keep stepping for about 1.5 s
+    # of wall time.  Every rank runs the same count (rank 0's clock decides) so the reduces pair.
+    ramp_steps = 0
+    t_ramp = time.perf_counter()
+    while True:
+        step(SEED + 900 + ramp_steps)
+        ramp_steps += 1
+        barrier()
+        go = torch.tensor([1 if time.perf_counter() - t_ramp < 1.5 and ramp_steps < 64 else 0],
+                          dtype=torch.int32, device="cuda")
+        if world > 1:
+            dist.broadcast(go, 0)
+        if not int(go.item()):
+            break
     for i in range(args.warmup):
         step(SEED + i)
     barrier()
@@ -297,19 +312,20 @@ def run_gpu(args, rank, world, local_rank):
     # BASELINE.json's second figure: time to image at 1080p, 256 spp (one extra, separately
     # timed frame; not part of `value`)
     f256, n256, s256 = multi_gpu.shard_samples(256, rank, world)
-    flush.zero_()
-    barrier()
-    e0 = torch.cuda.Event(enable_timing=True)
-    e1 = torch.cuda.Event(enable_timing=True)
-    e0.record()
-    ctx.reset()
-    ctx.trace(cam, n256, first_sample=f256, stride=s256, seed=SEED + 5000, flags=flags)
-    if world > 1:
-        multi_gpu.reduce_film(film, 0)
-    if rank == 0:
-        ctx.resolve()
-    e1.record()
-    barrier()
+    for timed in (False, True):  # one untimed frame first: the path pool grows to this job's size
+        flush.zero_()
+        barrier()
+        e0 = torch.cuda.Event(enable_timing=True)
+        e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        ctx.reset()
+        ctx.trace(cam, n256, first_sample=f256, stride=s256, seed=SEED + 5000 + timed, flags=flags)
+        if world > 1:
+            multi_gpu.reduce_film(film, 0)
+        if rank == 0:
+            ctx.resolve()
+        e1.record()
+        barrier()
     t256 = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(t256, op=dist.ReduceOp.MAX)
@@ -391,7 +407,7 @@ def run_gpu(args, rank, world, local_rank):
                            "scene_bytes": hs.nbytes(), "host_load_build_s": round(load_s, 2),
                            "sharding": "sample indices r, r+N, ... per rank; film reduce to rank 0",
                            "l2": "flushed between steps (256 MiB write)", "seed": SEED,
-                           "variant": args.variant,
+                           "variant": args.variant, "untimed_ramp_steps": ramp_steps,
                            "time_to_image_ms": total_ms / args.steps,
                            "time_to_image_1080p_256spp_ms": t256,
                            "mrays_per_s": float(segs.item()) / total_ms / 1e3},

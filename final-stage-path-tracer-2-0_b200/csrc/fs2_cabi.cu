@@ -261,10 +261,12 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   const uint32_t pix_cap = tiles_x * tiles_y * 128u;
   const unsigned long long total = (unsigned long long)pix_cap * tp.n_samples;
   unsigned long long pool = FS2_WF_MAX_PATHS;
-  if (ctx->tune >> 8) {
-    pool = (unsigned long long)(ctx->tune >> 8) << 10;  // FS2_TUNE bits 8..
-  } else if ((size_t)pool * 212 > ctx->wf_planes.bytes + ctx->wf_hit.bytes) {
-    // never take more than an eighth of what is free for the path state
+  if (ctx->tune >> 8) pool = (unsigned long long)(ctx->tune >> 8) << 10;  // FS2_TUNE bits 8..
+  if (pool > total) pool = total;
+  if (!(ctx->tune >> 8) && (size_t)pool * 212 > ctx->wf_planes.bytes + ctx->wf_hit.bytes) {
+    // the buffers have to grow: never take more than an eighth of what is free for the path
+    // state.  Only then — cudaMemGetInfo costs milliseconds when several processes share the
+    // driver, which showed as 35 -> 40 ms per frame at 8 GPUs when it ran on every call.
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
       unsigned long long fit = (free_b / 8) / 212;
@@ -272,7 +274,6 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
       if (pool > fit) pool = fit;
     }
   }
-  if (pool > total) pool = total;
   int pipes = (ctx->tune & 32u) || pool < (1u << 18) ? 1 : FS2_WF_PIPES;  // FS2_TUNE bit 5: one pipe
   const uint32_t cap = (uint32_t)(((pool + pipes - 1) / pipes + 127u) & ~127ull);
   int rc;
