@@ -323,7 +323,12 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_kernel, FS2_PH_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   const int persistent = ctx->sm_count * per_sm;  // one resident generation of CTAs
-  const uint32_t shade_blocks = cap / 128u;
+  // k_wf_shade's grid covers the live paths of the wave.  The live count never grows from one
+  // wave to the next (a finished path is replaced by at most one new one), so the count a
+  // k_wf_flip published for an earlier wave bounds it; once the camera paths run out the tail
+  // waves shrink and so do their grids (an empty 131 072-CTA grid alone costs 0.15 ms).
+  uint32_t live_bound[FS2_WF_PIPES];
+  for (int p = 0; p < FS2_WF_PIPES; p++) live_bound[p] = cap;
   bool done[FS2_WF_PIPES] = {};
   for (unsigned long long wave = 0; wave < max_waves; wave++) {
     int running = 0;
@@ -332,11 +337,14 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
       cudaEvent_t ev = ctx->wf_events[p * FS2_WF_AHEAD + wave % FS2_WF_AHEAD];
       if (wave >= FS2_WF_AHEAD) {
         CUDA_TRY(ctx, cudaEventSynchronize(ev));
-        if (*(volatile uint32_t*)(ctx->wf_host_live + p) == 0u) {
+        const uint32_t live = *(volatile uint32_t*)(ctx->wf_host_live + p);
+        if (live == 0u) {
           done[p] = true;
           continue;
         }
+        if (live < live_bound[p]) live_bound[p] = live;
       }
+      const uint32_t shade_blocks = (live_bound[p] + 127u) / 128u;
       running++;
       k_wf_flip<<<1, 1, 0, streams[p]>>>(B[p].counters, B[p].host_live);
       CUDA_TRY(ctx, cudaEventRecord(ev, streams[p]));
