@@ -256,7 +256,7 @@ int collect_timing(fs_ctx* ctx) {
 //    in a pinned host word, the host keeps FS2_WF_AHEAD waves enqueued per pipe (event ring)
 //    and stops enqueueing once a wave reported zero live paths; the waves already in the
 //    queue then exit at once.
-int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
+int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
   const uint32_t tiles_x = (uint32_t)(film.width + 15) / 16, tiles_y = (uint32_t)(film.height + 7) / 8;
   const uint32_t pix_cap = tiles_x * tiles_y * 128u;
   const unsigned long long total = (unsigned long long)pix_cap * tp.n_samples;
@@ -360,6 +360,18 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return FS_OK;
+}
+
+// A failure part-way leaves waves enqueued on both streams: drain them before reporting, so the
+// caller may free or reuse the film and the context's buffers.
+int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
+  int rc = launch_wavefront_waves(ctx, cb, film, tp);
+  if (rc) {
+    if (ctx->wf_stream) cudaStreamSynchronize(ctx->wf_stream);
+    cudaStreamSynchronize(ctx->stream);
+    cudaGetLastError();
+  }
+  return rc;
 }
 
 #include "fs2_build_host.inc"
