@@ -21,6 +21,7 @@
 #include "fs2_kernels.cuh"
 #include "fs2_build.cuh"
 #include "fs2_post.cuh"
+#include "fs2_selftest.cuh"
 #include "fs2_lbvh_build.h"
 
 using namespace fs2;
@@ -782,6 +783,30 @@ int fs_film_post(fs_ctx* ctx, const fs_post_params* pr, float* rgb, uint8_t* rgb
   if (rgb) CUDA_TRY(ctx, cudaMemcpyAsync(rgb, d_rgb, (size_t)n * 12, cudaMemcpyDeviceToHost, st));
   if (rgb8) CUDA_TRY(ctx, cudaMemcpyAsync(rgb8, d_rgb8, (size_t)n * 3, cudaMemcpyDeviceToHost, st));
   CUDA_TRY(ctx, cudaStreamSynchronize(st));
+  return FS_OK;
+}
+
+int fs_device_selftest(int device, uint32_t* words, uint32_t n_words) {
+  if (!words || n_words < FS2_SELFTEST_WORDS)
+    return fail(nullptr, FS_E_INVALID, "fs_device_selftest: need room for %d words", FS2_SELFTEST_WORDS);
+  cudaError_t e = cudaSetDevice(device);
+  void* buf = nullptr;
+  if (e == cudaSuccess) e = cudaMalloc(&buf, 1024);
+  if (e == cudaSuccess) {
+    float4* plane = (float4*)buf;
+    fs_tri_aux* aux = (fs_tri_aux*)((char*)buf + 64);
+    uint32_t* out = (uint32_t*)((char*)buf + 256);
+    k_selftest_pack<<<1, 1>>>(plane, aux);
+    k_selftest<<<1, 1>>>(plane, aux, out);
+    e = cudaGetLastError();
+    if (e == cudaSuccess)
+      e = cudaMemcpy(words, out, FS2_SELFTEST_WORDS * sizeof(uint32_t), cudaMemcpyDeviceToHost);
+  }
+  if (buf) cudaFree(buf);
+  if (e != cudaSuccess) {
+    cudaGetLastError();
+    return fail(nullptr, FS_E_CUDA, "fs_device_selftest: %s", cudaGetErrorString(e));
+  }
   return FS_OK;
 }
 

@@ -12,6 +12,7 @@ _SYMBOLS = {
     "fs_film_save": (C.c_int, [C.c_void_p, C.c_void_p]),
     "fs_film_load": (C.c_int, [C.c_void_p, C.c_void_p]),
     "fs_film_post": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_post_params), C.c_void_p, C.c_void_p]),
+    "fs_device_selftest": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32]),
     "fs_host_register": (C.c_int, [C.c_void_p, C.c_size_t]),
     "fs_host_unregister": (C.c_int, [C.c_void_p]),
     "fs_mesh_tree_build": (C.c_int, [C.c_int, C.c_void_p, C.c_uint32, C.c_void_p, C.c_void_p,

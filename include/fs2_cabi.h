@@ -308,6 +308,14 @@ typedef struct fs_post_params {
 } fs_post_params;
 int fs_film_post(fs_ctx* ctx, const fs_post_params* params, float* rgb, uint8_t* rgb8);
 
+/* Diagnostic: one device thread evaluates the known-answer inputs of the reference (fast
+ * inverse square root, plane / triangle / sphere / box intersections of two probe rays,
+ * normalize / reflect / refract / rotate, sphere-map coordinates, the xorshift64* stream from the
+ * reference's default seed, WritePixel's quantiser) with the device functions the kernels are
+ * built from and returns the raw 32-bit words (48 of them; layout in csrc/fs2_selftest.cuh).
+ * tests/test_gpu_kat.py compares them with the bits the unmodified reference prints. */
+int fs_device_selftest(int device, uint32_t* words, uint32_t n_words);
+
 int fs_get_stats(fs_ctx* ctx, fs_stats* out);
 int fs_reset_stats(fs_ctx* ctx);
 
