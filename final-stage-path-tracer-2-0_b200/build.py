@@ -68,7 +68,7 @@ def build_host(force=False):
     build_cuda()  # libfs2host.so links against the C ABI library next to it
     cmd = ["g++"] + GXX_FLAGS + ["-I" + os.path.join(REPO_DIR, "include"), "-I" + HOST,
                                  "-o", HOST_LIB] + srcs + ["-L" + PKG_DIR, "-lfs2cuda",
-                                                           "-Wl,-rpath,$ORIGIN", "-lpthread"]
+                                                           "-Wl,-rpath,$ORIGIN", "-lpthread", "-lz"]
     subprocess.run(cmd, check=True)
     return HOST_LIB
 

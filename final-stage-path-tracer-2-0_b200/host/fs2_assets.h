@@ -1,4 +1,4 @@
-// fs2_assets.h — .obj / .bmp / .hdr readers (see fs2_assets.cpp).
+// fs2_assets.h — .obj / .bmp / .hdr readers (fs2_assets.cpp) and the .exr reader (fs2_exr.cpp).
 #ifndef FS2_ASSETS_H_
 #define FS2_ASSETS_H_
 
@@ -24,6 +24,8 @@ struct Image {
 bool load_obj(const std::string& path, ObjData* out, std::string* error);
 bool load_bmp(const std::string& path, Image* out);
 bool load_hdr(const std::string& path, Image* out);
+// OpenEXR scan-line files (fs2_exr.cpp): HALF / FLOAT, NONE / RLE / ZIPS / ZIP; rows top to bottom.
+bool load_exr(const std::string& path, Image* out, std::string* error);
 
 }  // namespace fs2h
 #endif

@@ -330,5 +330,24 @@ void fs2h_set_seed(uint64_t seed) { base::SetTraceSeed(seed); }
 void fs2h_set_gpu_build(int device) { fs2h::gpu_build_device() = device; }
 float fs2h_gpu_build_ms() { return fs2h::gpu_build_ms(); }
 const char* fs2h_last_error() { return base::LastTraceError(); }
+// Texture readers by file extension (.bmp / .hdr / .exr), for tests: writes width, height and up
+// to cap_floats floats (3 per texel, rows in file order); returns 0, -1 unreadable, -2 too small.
+int fs2h_load_image(const char* path, uint32_t* width, uint32_t* height, float* rgb, size_t cap_floats) {
+  fs2h::Image img;
+  std::string p = path ? path : "", err;
+  auto ends = [&](const char* e) { return p.size() >= strlen(e) && p.compare(p.size() - strlen(e), strlen(e), e) == 0; };
+  bool ok = ends(".bmp") ? fs2h::load_bmp(p, &img)
+          : ends(".hdr") ? fs2h::load_hdr(p, &img)
+          : ends(".exr") ? fs2h::load_exr(p, &img, &err) : false;
+  if (!ok) {
+    fail_msg(("fs2h_load_image: " + p + ": " + (err.empty() ? "unreadable" : err)).c_str());
+    return -1;
+  }
+  *width = img.width;
+  *height = img.height;
+  if (img.rgb.size() > cap_floats) return -2;
+  if (rgb) memcpy(rgb, img.rgb.data(), img.rgb.size() * sizeof(float));
+  return 0;
+}
 
 }  // extern "C"

@@ -1,0 +1,256 @@
+// fs2_exr.cpp — OpenEXR texture reader of the host side.
+//
+// The reference reads .exr textures through tinyexr's LoadEXR (call site: reference
+// source/material.cpp:70-92: RGBA float out, rgb copied texel by texel in file row order).
+// tinyexr is a third-party header that is NOT in /root/reference (un-vendored), so this is a
+// restatement of the published OpenEXR 2 file layout, written for this project:
+//   magic 20000630, version 2 (tiled / deep / multi-part files are rejected),
+//   attribute list (channels, compression, dataWindow, lineOrder are read; the rest skipped),
+//   chunk offset table, scan-line chunks { int32 y, int32 size, data }.
+// Supported: pixel types HALF and FLOAT, compression NONE, RLE, ZIPS, ZIP (zlib + byte-delta
+// predictor + even/odd de-interleave), either line order, any dataWindow origin.  Channel
+// selection follows LoadEXR: R, G, B by name; a single-channel file becomes grey.
+// Row 0 of the result is the top scan line (dataWindow.min.y), as tinyexr returns it.
+#include <math.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <string.h>
+#include <zlib.h>
+
+#include <string>
+#include <vector>
+
+#include "fs2_assets.h"
+
+namespace fs2h {
+
+namespace {
+
+struct Reader {
+  const unsigned char* p;
+  const unsigned char* end;
+  bool ok = true;
+  bool need(size_t n) {
+    if ((size_t)(end - p) < n) ok = false;
+    return ok;
+  }
+  uint32_t u32() {
+    if (!need(4)) return 0;
+    uint32_t v = p[0] | p[1] << 8 | p[2] << 16 | (uint32_t)p[3] << 24;
+    p += 4;
+    return v;
+  }
+  uint64_t u64() {
+    uint64_t lo = u32(), hi = u32();
+    return lo | hi << 32;
+  }
+  uint8_t u8() {
+    if (!need(1)) return 0;
+    return *p++;
+  }
+  std::string str() {  // zero-terminated
+    std::string s;
+    while (need(1) && *p) s.push_back((char)*p++);
+    if (ok) p++;
+    return s;
+  }
+};
+
+float half_to_float(uint16_t h) {
+  uint32_t sign = (uint32_t)(h >> 15) << 31, exp = (h >> 10) & 31u, man = h & 1023u, w;
+  if (exp == 0) {
+    if (man == 0) {
+      w = sign;
+    } else {  // subnormal half: normalise
+      int e = -1;
+      do {
+        man <<= 1;
+        e++;
+      } while (!(man & 1024u));
+      w = sign | (uint32_t)(127 - 15 - e) << 23 | (man & 1023u) << 13;
+    }
+  } else if (exp == 31) {
+    w = sign | 0x7F800000u | man << 13;
+  } else {
+    w = sign | (exp + 127 - 15) << 23 | man << 13;
+  }
+  float f;
+  memcpy(&f, &w, 4);
+  return f;
+}
+
+struct Channel {
+  std::string name;
+  int type;       // 1 half, 2 float
+  size_t offset;  // byte offset of the channel's run inside one scan line
+};
+
+// OpenEXR's post-processing of RLE / ZIP data: running byte sum, then even/odd interleave.
+void unpredict(std::vector<unsigned char>& t, std::vector<unsigned char>& out) {
+  for (size_t i = 1; i < t.size(); i++) t[i] = (unsigned char)(t[i - 1] + t[i] - 128);
+  const size_t n = t.size(), half = (n + 1) / 2;
+  out.resize(n);
+  for (size_t i = 0; i < half; i++) {
+    out[2 * i] = t[i];
+    if (2 * i + 1 < n) out[2 * i + 1] = t[half + i];
+  }
+}
+
+bool rle_decode(const unsigned char* s, size_t n, std::vector<unsigned char>& out, size_t want) {
+  out.clear();
+  const unsigned char* e = s + n;
+  while (s < e) {
+    int count = (signed char)*s++;
+    if (count < 0) {
+      size_t k = (size_t)(-count);
+      if ((size_t)(e - s) < k) return false;
+      out.insert(out.end(), s, s + k);
+      s += k;
+    } else {
+      if (s >= e) return false;
+      out.insert(out.end(), (size_t)count + 1, *s++);
+    }
+    if (out.size() > want) return false;
+  }
+  return out.size() == want;
+}
+
+}  // namespace
+
+bool load_exr(const std::string& path, Image* out, std::string* error) {
+  auto fail = [&](const char* why) {
+    if (error) *error = why;
+    return false;
+  };
+  std::vector<unsigned char> data;
+  {
+    FILE* f = fopen(path.c_str(), "rb");
+    if (!f) return fail("cannot open file");
+    fseek(f, 0, SEEK_END);
+    long n = ftell(f);
+    fseek(f, 0, SEEK_SET);
+    data.resize(n > 0 ? (size_t)n : 0);
+    size_t got = data.empty() ? 0 : fread(data.data(), 1, data.size(), f);
+    fclose(f);
+    data.resize(got);
+  }
+  Reader r{data.data(), data.data() + data.size()};
+  if (r.u32() != 20000630u) return fail("not an OpenEXR file");
+  uint32_t version = r.u32();
+  if ((version & 0xFFu) != 2u) return fail("unsupported OpenEXR version");
+  if (version & (0x200u | 0x800u | 0x1000u)) return fail("tiled, deep and multi-part files are not supported");
+  std::vector<Channel> channels;
+  int compression = -1, line_order = 0;
+  int32_t win[4] = {0, 0, -1, -1};
+  bool have_window = false;
+  for (;;) {  // attribute list, closed by an empty name
+    std::string name = r.str();
+    if (!r.ok) return fail("truncated header");
+    if (name.empty()) break;
+    std::string type = r.str();
+    uint32_t size = r.u32();
+    if (!r.need(size)) return fail("truncated header");
+    Reader a{r.p, r.p + size};
+    r.p += size;
+    if (name == "channels") {
+      for (;;) {
+        std::string cn = a.str();
+        if (!a.ok) return fail("bad channel list");
+        if (cn.empty()) break;
+        Channel c;
+        c.name = cn;
+        c.type = (int)a.u32();
+        a.u8();  // pLinear
+        a.u8(), a.u8(), a.u8();
+        uint32_t xs = a.u32(), ys = a.u32();
+        if (!a.ok) return fail("bad channel list");
+        if (xs != 1 || ys != 1) return fail("sub-sampled channels are not supported");
+        if (c.type != 1 && c.type != 2) return fail("only HALF and FLOAT channels are supported");
+        c.offset = 0;
+        channels.push_back(c);
+      }
+    } else if (name == "compression") {
+      compression = a.u8();
+    } else if (name == "dataWindow") {
+      for (int i = 0; i < 4; i++) win[i] = (int32_t)a.u32();
+      have_window = a.ok;
+    } else if (name == "lineOrder") {
+      line_order = a.u8();
+    }
+  }
+  if (channels.empty() || compression < 0 || !have_window) return fail("missing required attribute");
+  if (compression > 3) return fail("only NONE, RLE, ZIPS and ZIP compression are supported");
+  if (line_order > 1) return fail("unsupported line order");
+  const long w = (long)win[2] - win[0] + 1, h = (long)win[3] - win[1] + 1;
+  if (w <= 0 || h <= 0 || w > 65536 || h > 65536) return fail("bad data window");
+  size_t line_bytes = 0;
+  for (Channel& c : channels) {
+    c.offset = line_bytes;
+    line_bytes += (size_t)w * (c.type == 1 ? 2 : 4);
+  }
+  // LoadEXR's channel choice
+  int pick[3] = {-1, -1, -1};
+  for (size_t i = 0; i < channels.size(); i++) {
+    if (channels[i].name == "R") pick[0] = (int)i;
+    if (channels[i].name == "G") pick[1] = (int)i;
+    if (channels[i].name == "B") pick[2] = (int)i;
+  }
+  if (pick[0] < 0 || pick[1] < 0 || pick[2] < 0) {
+    if (channels.size() != 1) return fail("R, G or B channel not found");
+    pick[0] = pick[1] = pick[2] = 0;
+  }
+  const int lines_per_block = compression == 3 ? 16 : 1;
+  const size_t blocks = ((size_t)h + lines_per_block - 1) / lines_per_block;
+  std::vector<uint64_t> offsets(blocks);
+  for (uint64_t& o : offsets) o = r.u64();
+  if (!r.ok) return fail("truncated offset table");
+  out->width = (uint32_t)w;
+  out->height = (uint32_t)h;
+  out->rgb.assign((size_t)w * h * 3, 0.f);
+  std::vector<unsigned char> tmp, raw;
+  for (size_t b = 0; b < blocks; b++) {
+    if (offsets[b] > data.size()) return fail("bad chunk offset");
+    Reader c{data.data() + offsets[b], data.data() + data.size()};
+    int32_t y0 = (int32_t)c.u32();
+    uint32_t size = c.u32();
+    if (!c.ok || !c.need(size)) return fail("truncated chunk");
+    long row0 = (long)y0 - win[1];
+    if (row0 < 0 || row0 >= h) return fail("chunk outside the data window");
+    long rows = h - row0 < lines_per_block ? h - row0 : lines_per_block;
+    const size_t want = line_bytes * (size_t)rows;
+    const unsigned char* px = c.p;
+    if (compression != 0 && size < want) {  // a chunk that did not shrink is stored raw
+      if (compression == 1) {
+        if (!rle_decode(c.p, size, tmp, want)) return fail("bad RLE data");
+      } else {
+        tmp.resize(want);
+        uLongf got = (uLongf)want;
+        if (uncompress(tmp.data(), &got, c.p, size) != Z_OK || got != want) return fail("bad ZIP data");
+      }
+      unpredict(tmp, raw);
+      px = raw.data();
+    } else if (size != want) {
+      return fail("bad chunk size");
+    }
+    for (long k = 0; k < rows; k++) {
+      const unsigned char* line = px + (size_t)k * line_bytes;
+      float* dst = &out->rgb[(size_t)(row0 + k) * w * 3];
+      for (int ch = 0; ch < 3; ch++) {
+        const Channel& cc = channels[pick[ch]];
+        const unsigned char* s = line + cc.offset;
+        for (long x = 0; x < w; x++) {
+          float v;
+          if (cc.type == 1) {
+            v = half_to_float((uint16_t)(s[2 * x] | s[2 * x + 1] << 8));
+          } else {
+            memcpy(&v, s + 4 * x, 4);
+          }
+          dst[3 * x + ch] = v;
+        }
+      }
+    }
+  }
+  return true;
+}
+
+}  // namespace fs2h

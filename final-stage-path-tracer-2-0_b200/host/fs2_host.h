@@ -92,8 +92,8 @@ class DiffuseMaterial : public Material {
   DiffuseMaterial();
   explicit DiffuseMaterial(const vector3& diffuse);
   explicit DiffuseMaterial(const std::string& filename, float32 tex_scale = 1.0f);
-  // .bmp as in the reference; .hdr (Radiance RGBE) is an extension; .exr is not supported
-  // in this build (the reference reads it through the vendored tinyexr).
+  // .bmp and .exr as in the reference (.exr: scan-line HALF / FLOAT files, host/fs2_exr.cpp);
+  // .hdr (Radiance RGBE) is an extension.
   void LoadDiffuseTexture(const std::string& filename, float32 tex_scale = 1.0f);
 
  protected:

@@ -101,8 +101,14 @@ void DiffuseMaterial::LoadDiffuseTexture(const std::string& filename, float32 te
   } else if (ends_with(filename, ".hdr")) {
     ok = load_hdr(filename, &impl_->texture);
   } else if (ends_with(filename, ".exr")) {
-    printf("Failed to load %s. Errors: .exr textures are not supported by this build.\n",
-           filename.c_str());
+    // reference source/material.cpp:70-92 (LoadEXR, then rgb of every texel in file row order)
+    std::string errors;
+    ok = load_exr(filename, &impl_->texture, &errors);
+    if (ok)
+      printf("Loaded %s with dims: <%i, %i>.\n", filename.c_str(), (int)impl_->texture.width,
+             (int)impl_->texture.height);
+    else
+      printf("Failed to load %s. Errors: %s.\n", filename.c_str(), errors.c_str());
   }
   if (!ok) impl_->texture = Image();
 }

@@ -1,0 +1,115 @@
+"""the .exr texture reader of the host side (host/fs2_exr.cpp) against
+files written by tests/exr_write.py from the published OpenEXR layout.  The reference reads .exr
+through tinyexr's LoadEXR (source/material.cpp:70-92), a third-party header that is not in
+/root/reference, so the format specification is the anchor: values must come back exactly
+(HALF -> float conversion is exact), rows top to bottom, R / G / B picked by name."""
+import ctypes as C
+import os
+
+import numpy as np
+import pytest
+
+from exr_write import write_exr
+from fs2_b200 import host
+
+
+def _load(path):
+    lib = host.load_host_library()
+    lib.fs2h_load_image.restype = C.c_int
+    lib.fs2h_load_image.argtypes = [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32),
+                                    C.c_void_p, C.c_size_t]
+    w, h = C.c_uint32(), C.c_uint32()
+    buf = np.zeros(1 << 20, np.float32)
+    rc = lib.fs2h_load_image(path.encode(), C.byref(w), C.byref(h), buf.ctypes.data_as(C.c_void_p), buf.size)
+    if rc != 0:
+        return rc, None
+    return 0, buf[: w.value * h.value * 3].reshape(h.value, w.value, 3).copy()
+
+
+def _image(h, w, dtype, seed):
+    rng = np.random.default_rng(seed)
+    img = (rng.random((h, w, 3)) * 4.0).astype(dtype)
+    img[0, 0] = (0.0, 1.0, 65504.0 if dtype == np.float16 else 1e30)
+    img[h // 2, : w // 2] = 0.25  # runs, for RLE
+    return img
+
+
+@pytest.mark.parametrize("comp", ["none", "rle", "zips", "zip"])
+@pytest.mark.parametrize("dtype", [np.float16, np.float32])
+def test_exr_round_trip(tmp_path, comp, dtype):
+    h, w = 37, 29  # not a multiple of ZIP's 16-line blocks
+    img = _image(h, w, dtype, 5)
+    path = str(tmp_path / "t.exr")
+    write_exr(path, {"R": img[..., 0], "G": img[..., 1], "B": img[..., 2],
+                     "A": np.ones((h, w), dtype)}, comp=comp)
+    rc, got = _load(path)
+    assert rc == 0
+    assert got.shape == (h, w, 3)
+    assert np.array_equal(got, img.astype(np.float32))
+
+
+def test_exr_decreasing_line_order_and_window_origin(tmp_path):
+    h, w = 20, 13
+    img = _image(h, w, np.float16, 9)
+    path = str(tmp_path / "d.exr")
+    write_exr(path, {"B": img[..., 2], "G": img[..., 1], "R": img[..., 0]}, comp="zip",
+              origin=(-7, 100), decreasing=True)
+    rc, got = _load(path)
+    assert rc == 0 and np.array_equal(got, img.astype(np.float32))
+
+
+def test_exr_single_channel_becomes_grey_and_mixed_types(tmp_path):
+    y = _image(9, 11, np.float32, 2)[..., 0]
+    path = str(tmp_path / "y.exr")
+    write_exr(path, {"Y": y}, comp="zips")
+    rc, got = _load(path)
+    assert rc == 0 and all(np.array_equal(got[..., c], y) for c in range(3))
+    img = _image(9, 11, np.float32, 3)
+    write_exr(path, {"R": img[..., 0].astype(np.float16), "G": img[..., 1], "B": img[..., 2],
+                     "Z": img[..., 0]}, comp="rle")
+    rc, got = _load(path)
+    assert rc == 0
+    assert np.array_equal(got[..., 0], img[..., 0].astype(np.float16).astype(np.float32))
+    assert np.array_equal(got[..., 1:], img[..., 1:])
+
+
+def test_exr_subnormal_and_special_halves(tmp_path):
+    bits = np.array([[0x0001, 0x03FF, 0x0400, 0x8001, 0x7C00, 0xFC00, 0x3C00, 0x0000]], np.uint16)
+    half = bits.view(np.float16)
+    path = str(tmp_path / "s.exr")
+    write_exr(path, {"R": half, "G": half, "B": half})
+    rc, got = _load(path)
+    assert rc == 0
+    assert np.array_equal(got[..., 0].view(np.uint32), half.astype(np.float32).view(np.uint32))
+
+
+def test_exr_rejects_damaged_files(tmp_path):
+    img = _image(16, 16, np.float16, 1)
+    path = str(tmp_path / "ok.exr")
+    write_exr(path, {"R": img[..., 0], "G": img[..., 1], "B": img[..., 2]}, comp="zip")
+    raw = open(path, "rb").read()
+    for name, data in (("short", raw[: len(raw) // 2]), ("magic", b"\0" + raw[1:]),
+                       ("tiled", raw[:5] + b"\x02" + raw[6:]), ("empty", b"")):
+        p = str(tmp_path / (name + ".exr"))
+        open(p, "wb").write(data)
+        rc, _ = _load(p)
+        assert rc == -1, name
+    assert b"fs2h_load_image" in host.load_host_library().fs2h_last_error()
+    rc, _ = _load(str(tmp_path / "missing.exr"))
+    assert rc == -1
+
+
+def test_scene_with_exr_texture_loads(tmp_path):
+    """A material block with an .exr texture ends up in the flattened scene's texels."""
+    img = _image(8, 8, np.float16, 4)
+    write_exr(str(tmp_path / "tex.exr"), {"R": img[..., 0], "G": img[..., 1], "B": img[..., 2]}, comp="zip")
+    scene = tmp_path / "s.scene"
+    scene.write_text(
+        "material m\n{\n color 1 1 1\n texture_scale 2\n texture %s\n}\n"
+        "sphere\n{\n material m\n position 0 0 0\n radius 1\n}\n" % (tmp_path / "tex.exr"))
+    hs = host.HostScene(str(scene))
+    flat = hs.to_flat()
+    tex = np.asarray(flat.texels, np.float32).reshape(-1)
+    want = img.astype(np.float32).reshape(-1)
+    assert tex.size >= want.size
+    assert any(np.array_equal(tex[i:i + want.size], want) for i in range(0, tex.size - want.size + 1, 3))
