@@ -8,7 +8,7 @@
 // --bloom strength[,threshold[,radius]], --flare strength[,ghosts]).
 // Written against the mirrored API of host/fs2_host.h only.
 //
-//   fs2_render -f scene.scene -w 1920 -h 1080 --spp 64 --out image.ppm [--pfm mean.pfm]
+//   fs2_render -f scene.scene -w 1920 -h 1080 --spp 64 --out image.ppm [--pfm mean.pfm] [--exr mean.exr]
 #include <chrono>
 #include <stdio.h>
 #include <stdlib.h>
@@ -52,7 +52,7 @@ static bool write_pfm(const std::string& path, DisplayFrame* f) {
 }
 
 int main(int argc, char** argv) {
-  std::string file, out = "fs2_render.ppm", pfm, checkpoint, resume;
+  std::string file, out = "fs2_render.ppm", pfm, exr, checkpoint, resume;
   uint32 width = 800, height = 480, spp = 16;  // 800x480: source/main.cpp:53-54
   uint64 seed = 1;
   int device = 0;
@@ -68,6 +68,7 @@ int main(int argc, char** argv) {
     else if (!strcmp(a, "--device")) device = atoi(next());
     else if (!strcmp(a, "--out")) out = next();
     else if (!strcmp(a, "--pfm")) pfm = next();
+    else if (!strcmp(a, "--exr")) exr = next();
     else if (!strcmp(a, "--fast")) fast = true;
     else if (!strcmp(a, "--checkpoint")) checkpoint = next();
     else if (!strcmp(a, "--resume")) resume = next();
@@ -90,7 +91,7 @@ int main(int argc, char** argv) {
   }
   if (file.empty()) {  // source/main.cpp:78-81
     fprintf(stderr, "usage: fs2_render -f <scene file> [-w W] [-h H] [--spp N] [--seed S] "
-                    "[--device D] [--out image.ppm] [--pfm mean.pfm] [--focus x,y] [--fast] "
+                    "[--device D] [--out image.ppm] [--pfm mean.pfm] [--exr mean.exr] [--focus x,y] [--fast] "
                     "[--resume film.ckpt] [--checkpoint film.ckpt] [--post-out image.ppm "
                     "[--denoise passes] [--bloom strength[,threshold[,radius]]] "
                     "[--flare strength[,ghosts]]]\n");
@@ -141,6 +142,10 @@ int main(int argc, char** argv) {
       fprintf(stderr, "cannot write %s\n", post_out.c_str());
       return 1;
     }
+  }
+  if (!exr.empty() && !SaveFrameEXR(&frame, exr.c_str())) {
+    fprintf(stderr, "cannot write %s\n", exr.c_str());
+    return 1;
   }
   if (!pfm.empty() && !write_pfm(pfm, &frame)) {
     fprintf(stderr, "cannot write %s\n", pfm.c_str());

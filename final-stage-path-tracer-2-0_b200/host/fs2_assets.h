@@ -26,6 +26,8 @@ bool load_bmp(const std::string& path, Image* out);
 bool load_hdr(const std::string& path, Image* out);
 // OpenEXR scan-line files (fs2_exr.cpp): HALF / FLOAT, NONE / RLE / ZIPS / ZIP; rows top to bottom.
 bool load_exr(const std::string& path, Image* out, std::string* error);
+// FLOAT B/G/R, ZIP-compressed scan-line file; bottom_up: row 0 of rgb is the bottom scan line.
+bool save_exr(const std::string& path, uint32_t w, uint32_t h, const float* rgb, bool bottom_up);
 
 }  // namespace fs2h
 #endif

@@ -206,6 +206,11 @@ bool PostProcessFrame(DisplayFrame* frame, const PostProcess& post, float* rgb, 
   return true;
 }
 
+bool SaveFrameEXR(DisplayFrame* frame, const char* path) {
+  if (!frame || !path) return false;
+  return fs2h::save_exr(path, frame->GetWidth(), frame->GetHeight(), frame->GetRenderTarget(), true);
+}
+
 bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path) {
   TraceState& st = state();
   if (!frame || !path || !st.ctx || st.frame != frame->impl() || frame->impl()->device_dirty) {
@@ -330,6 +335,9 @@ void fs2h_set_seed(uint64_t seed) { base::SetTraceSeed(seed); }
 void fs2h_set_gpu_build(int device) { fs2h::gpu_build_device() = device; }
 float fs2h_gpu_build_ms() { return fs2h::gpu_build_ms(); }
 const char* fs2h_last_error() { return base::LastTraceError(); }
+int fs2h_save_exr(const char* path, uint32_t width, uint32_t height, const float* rgb, int bottom_up) {
+  return path && fs2h::save_exr(path, width, height, rgb, bottom_up != 0) ? 0 : -1;
+}
 // Texture readers by file extension (.bmp / .hdr / .exr), for tests: writes width, height and up
 // to cap_floats floats (3 per texel, rows in file order); returns 0, -1 unreadable, -2 too small.
 int fs2h_load_image(const char* path, uint32_t* width, uint32_t* height, float* rgb, size_t cap_floats) {

@@ -253,4 +253,97 @@ bool load_exr(const std::string& path, Image* out, std::string* error) {
   return true;
 }
 
+// Writer for the headless front end: FLOAT B, G, R channels, ZIP
+// compression (16-line blocks; a block that does not shrink is stored raw), increasing line
+// order.  rgb: 3 floats per pixel; `bottom_up` says row 0 of rgb is the bottom scan line (the
+// film's order) and is flipped so that the file's first line is the top of the picture.
+bool save_exr(const std::string& path, uint32_t w, uint32_t h, const float* rgb, bool bottom_up) {
+  if (!w || !h || !rgb) return false;
+  std::vector<unsigned char> head;
+  auto put32 = [&](std::vector<unsigned char>& v, uint32_t x) {
+    for (int i = 0; i < 4; i++) v.push_back((unsigned char)(x >> (8 * i)));
+  };
+  auto puts = [&](const char* t) {
+    while (*t) head.push_back((unsigned char)*t++);
+    head.push_back(0);
+  };
+  auto attr = [&](const char* name, const char* type, const std::vector<unsigned char>& payload) {
+    puts(name);
+    puts(type);
+    put32(head, (uint32_t)payload.size());
+    head.insert(head.end(), payload.begin(), payload.end());
+  };
+  put32(head, 20000630u);
+  put32(head, 2u);
+  {
+    std::vector<unsigned char> ch;
+    for (const char* n : {"B", "G", "R"}) {
+      ch.push_back((unsigned char)n[0]);
+      ch.push_back(0);
+      put32(ch, 2u);  // FLOAT
+      put32(ch, 0u);  // pLinear + reserved
+      put32(ch, 1u);
+      put32(ch, 1u);
+    }
+    ch.push_back(0);
+    attr("channels", "chlist", ch);
+  }
+  attr("compression", "compression", {3});
+  std::vector<unsigned char> box;
+  put32(box, 0u), put32(box, 0u), put32(box, w - 1), put32(box, h - 1);
+  attr("dataWindow", "box2i", box);
+  attr("displayWindow", "box2i", box);
+  attr("lineOrder", "lineOrder", {0});
+  const float one = 1.0f, zero = 0.0f;
+  std::vector<unsigned char> f1((const unsigned char*)&one, (const unsigned char*)&one + 4);
+  std::vector<unsigned char> f0((const unsigned char*)&zero, (const unsigned char*)&zero + 4);
+  attr("pixelAspectRatio", "float", f1);
+  std::vector<unsigned char> v2(f0);
+  v2.insert(v2.end(), f0.begin(), f0.end());
+  attr("screenWindowCenter", "v2f", v2);
+  attr("screenWindowWidth", "float", f1);
+  head.push_back(0);
+  const uint32_t blocks = (h + 15) / 16;
+  const size_t line_bytes = (size_t)w * 12;
+  std::vector<std::vector<unsigned char>> chunks(blocks);
+  std::vector<unsigned char> raw, split, packed;
+  for (uint32_t b = 0; b < blocks; b++) {
+    const uint32_t r0 = b * 16, rows = h - r0 < 16 ? h - r0 : 16;
+    raw.resize(line_bytes * rows);
+    for (uint32_t k = 0; k < rows; k++) {
+      const uint32_t src_row = bottom_up ? h - 1 - (r0 + k) : r0 + k;
+      const float* src = rgb + (size_t)src_row * w * 3;
+      float* line = (float*)(raw.data() + (size_t)k * line_bytes);
+      for (uint32_t x = 0; x < w; x++) {  // channel runs in alphabetical order: B, G, R
+        line[x] = src[3 * x + 2];
+        line[w + x] = src[3 * x + 1];
+        line[2 * (size_t)w + x] = src[3 * x];
+      }
+    }
+    // even/odd split, byte delta, deflate
+    const size_t n = raw.size(), half = (n + 1) / 2;
+    split.resize(n);
+    for (size_t i = 0; i < n; i++) split[(i & 1) ? half + i / 2 : i / 2] = raw[i];
+    for (size_t i = n - 1; i > 0; i--) split[i] = (unsigned char)(split[i] - split[i - 1] + 128);
+    uLongf cap = compressBound((uLong)n);
+    packed.resize(cap);
+    const bool shrunk = compress2(packed.data(), &cap, split.data(), (uLong)n, 6) == Z_OK && cap < n;
+    const std::vector<unsigned char>& body = shrunk ? packed : raw;
+    const size_t body_n = shrunk ? (size_t)cap : n;
+    put32(chunks[b], r0);
+    put32(chunks[b], (uint32_t)body_n);
+    chunks[b].insert(chunks[b].end(), body.begin(), body.begin() + body_n);
+  }
+  FILE* f = fopen(path.c_str(), "wb");
+  if (!f) return false;
+  bool ok = fwrite(head.data(), 1, head.size(), f) == head.size();
+  uint64_t pos = head.size() + 8ull * blocks;
+  for (uint32_t b = 0; b < blocks && ok; b++) {
+    ok = fwrite(&pos, 8, 1, f) == 1;  // little-endian host
+    pos += chunks[b].size();
+  }
+  for (uint32_t b = 0; b < blocks && ok; b++) ok = fwrite(chunks[b].data(), 1, chunks[b].size(), f) == chunks[b].size();
+  return fclose(f) == 0 && ok;
+}
+
 }  // namespace fs2h

@@ -268,6 +268,10 @@ const char* LastTraceError();
 bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path);
 bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path);
 
+// Writes the frame's float mean image as an OpenEXR file (FLOAT R, G, B, ZIP; host/fs2_exr.cpp):
+// the lossless output of the headless front end next to PPM / PFM.
+bool SaveFrameEXR(DisplayFrame* frame, const char* path);
+
 // Film post-processing on the device (fs_film_post): guided a-trous denoise, bloom and flare of
 // the frame's resolved image, using its normal / depth / material-id planes (frame.h:86-91).
 // The reference's README describes these stages, its code has none.  Outputs (either may be

@@ -113,3 +113,49 @@ def test_scene_with_exr_texture_loads(tmp_path):
     want = img.astype(np.float32).reshape(-1)
     assert tex.size >= want.size
     assert any(np.array_equal(tex[i:i + want.size], want) for i in range(0, tex.size - want.size + 1, 3))
+
+
+def test_exr_writer_round_trips_through_the_reader(tmp_path):
+    """save_exr (the CLI's --exr output: FLOAT B/G/R, ZIP, film rows bottom-up) read back by
+    load_exr: exact values, top row first."""
+    lib = host.load_host_library()
+    lib.fs2h_save_exr.restype = C.c_int
+    lib.fs2h_save_exr.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]
+    for h, w, seed in ((37, 29, 1), (16, 8, 2), (1, 1, 3)):
+        img = _image(h, w, np.float32, seed) if h > 1 else np.array([[[0.5, 2.0, -1.0]]], np.float32)
+        if h > 1:
+            img[3:30, :, :] = 0.125  # compressible blocks next to random (stored raw) ones
+        path = str(tmp_path / ("w%d.exr" % seed))
+        for bottom_up in (0, 1):
+            assert lib.fs2h_save_exr(path.encode(), w, h, img.ctypes.data_as(C.c_void_p), bottom_up) == 0
+            rc, got = _load(path)
+            assert rc == 0
+            assert np.array_equal(got, img[::-1] if bottom_up else img)
+    assert lib.fs2h_save_exr(str(tmp_path / "no" / "dir.exr").encode(), 2, 2,
+                             np.zeros(12, np.float32).ctypes.data_as(C.c_void_p), 0) != 0
+
+
+def test_exr_against_an_independent_codec(tmp_path):
+    """Cross-check with the OpenEXR library inside OpenCV (when the image has it): files of
+    tests/exr_write.py and of save_exr read by OpenCV, OpenCV's own file read by load_exr."""
+    os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
+    cv2 = pytest.importorskip("cv2")
+    img = _image(37, 29, np.float32, 11)
+    img[0, 0] = (0.0, 1.0, 1e30)
+    p = str(tmp_path / "x.exr")
+    if not cv2.imwrite(p, img[..., ::-1].copy()):
+        pytest.skip("this OpenCV build has no OpenEXR codec")
+    rc, got = _load(p)  # OpenCV writer -> our reader
+    assert rc == 0 and np.array_equal(got, img)
+    for comp in ("none", "rle", "zips", "zip"):  # test writer -> OpenCV reader
+        for dt in (np.float16, np.float32):
+            im = img.clip(0, 60000).astype(dt)
+            write_exr(p, {"R": im[..., 0], "G": im[..., 1], "B": im[..., 2]}, comp=comp)
+            ref = cv2.imread(p, cv2.IMREAD_UNCHANGED)
+            assert ref is not None and np.array_equal(ref[..., ::-1].astype(np.float32), im.astype(np.float32))
+    lib = host.load_host_library()  # our writer -> OpenCV reader
+    lib.fs2h_save_exr.restype = C.c_int
+    lib.fs2h_save_exr.argtypes = [C.c_char_p, C.c_uint32, C.c_uint32, C.c_void_p, C.c_int]
+    assert lib.fs2h_save_exr(p.encode(), 29, 37, img.ctypes.data_as(C.c_void_p), 0) == 0
+    ref = cv2.imread(p, cv2.IMREAD_UNCHANGED)
+    assert ref is not None and np.array_equal(ref[..., ::-1], img)
