@@ -83,3 +83,24 @@ def test_cli_post_processing_output(tmp_path):
     bad = subprocess.run(common + ["--post-out", str(tmp_path / "x.ppm"), "--denoise", "99"],
                          capture_output=True, text=True)
     assert bad.returncode != 0 and "post-processing failed" in bad.stderr
+
+
+def test_cli_exr_output_equals_the_pfm(tmp_path):
+    """--exr writes the same float mean image as --pfm (lossless, top row first in the file)."""
+    import ctypes as C
+    from fs2_b200 import host
+    exe = build.build_cli()
+    scene = gen_scenes.generate(str(tmp_path), ["demo"])["demo"]
+    pfm, exr = str(tmp_path / "o.pfm"), str(tmp_path / "o.exr")
+    r = subprocess.run([exe, "-f", scene, "-w", "72", "-h", "40", "--spp", "4", "--out", str(tmp_path / "o.ppm"),
+                        "--pfm", pfm, "--exr", exr], capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
+    mean = np.frombuffer(open(pfm, "rb").read()[len(b"PF\n72 40\n-1.0\n"):], np.float32).reshape(40, 72, 3)
+    lib = host.load_host_library()
+    lib.fs2h_load_image.restype = C.c_int
+    lib.fs2h_load_image.argtypes = [C.c_char_p, C.POINTER(C.c_uint32), C.POINTER(C.c_uint32), C.c_void_p, C.c_size_t]
+    w, h = C.c_uint32(), C.c_uint32()
+    buf = np.zeros(72 * 40 * 3, np.float32)
+    assert lib.fs2h_load_image(exr.encode(), C.byref(w), C.byref(h), buf.ctypes.data_as(C.c_void_p), buf.size) == 0
+    assert (w.value, h.value) == (72, 40)
+    assert np.array_equal(buf.reshape(40, 72, 3)[::-1], mean)
