@@ -182,7 +182,7 @@ bool load_exr(const std::string& path, Image* out, std::string* error) {
   if (compression > 3) return fail("only NONE, RLE, ZIPS and ZIP compression are supported");
   if (line_order > 1) return fail("unsupported line order");
   const long w = (long)win[2] - win[0] + 1, h = (long)win[3] - win[1] + 1;
-  if (w <= 0 || h <= 0 || w > 65536 || h > 65536) return fail("bad data window");
+  if (w <= 0 || h <= 0 || w > 65536 || h > 65536 || w * h > (1L << 28)) return fail("bad data window");
   size_t line_bytes = 0;
   for (Channel& c : channels) {
     c.offset = line_bytes;
@@ -204,6 +204,8 @@ bool load_exr(const std::string& path, Image* out, std::string* error) {
   std::vector<uint64_t> offsets(blocks);
   for (uint64_t& o : offsets) o = r.u64();
   if (!r.ok) return fail("truncated offset table");
+  // every scan line needs at least its chunk header in the file: refuse windows the file cannot hold
+  if (blocks * 8 > data.size()) return fail("data window larger than the file");
   out->width = (uint32_t)w;
   out->height = (uint32_t)h;
   out->rgb.assign((size_t)w * h * 3, 0.f);

@@ -159,3 +159,26 @@ def test_exr_against_an_independent_codec(tmp_path):
     assert lib.fs2h_save_exr(p.encode(), 29, 37, img.ctypes.data_as(C.c_void_p), 0) == 0
     ref = cv2.imread(p, cv2.IMREAD_UNCHANGED)
     assert ref is not None and np.array_equal(ref[..., ::-1], img)
+
+
+def test_exr_reader_survives_corrupted_files(tmp_path):
+    """Random byte damage anywhere in a valid file: the reader answers (image or error), it
+    never crashes or over-allocates."""
+    img = _image(24, 17, np.float16, 6)
+    good = str(tmp_path / "g.exr")
+    rng = np.random.default_rng(123)
+    for comp in ("none", "rle", "zip"):
+        write_exr(good, {"R": img[..., 0], "G": img[..., 1], "B": img[..., 2]}, comp=comp)
+        raw = bytearray(open(good, "rb").read())
+        for trial in range(150):
+            bad = bytearray(raw)
+            for _ in range(int(rng.integers(1, 6))):
+                bad[int(rng.integers(0, len(bad)))] = int(rng.integers(0, 256))
+            if trial % 10 == 0:
+                bad = bad[: int(rng.integers(0, len(bad)))]
+            p = str(tmp_path / "bad.exr")
+            open(p, "wb").write(bytes(bad))
+            rc, got = _load(p)
+            assert rc in (0, -1, -2)
+            if rc == 0:
+                assert got.ndim == 3 and got.shape[2] == 3
