@@ -23,6 +23,10 @@ bool read_file(const std::string& path, std::vector<char>* data) {
   fseek(f, 0, SEEK_END);
   long n = ftell(f);
   fseek(f, 0, SEEK_SET);
+  if (n < 0 || n > (1L << 34)) {  // a directory opens and reports LONG_MAX; no asset is 16 GB
+    fclose(f);
+    return false;
+  }
   data->resize((size_t)n + 1);
   size_t got = n ? fread(data->data(), 1, (size_t)n, f) : 0;
   fclose(f);

@@ -129,7 +129,11 @@ bool load_exr(const std::string& path, Image* out, std::string* error) {
     fseek(f, 0, SEEK_END);
     long n = ftell(f);
     fseek(f, 0, SEEK_SET);
-    data.resize(n > 0 ? (size_t)n : 0);
+    if (n < 0 || n > (1L << 34)) {  // a directory opens and reports LONG_MAX
+      fclose(f);
+      return fail("not a regular file");
+    }
+    data.resize((size_t)n);
     size_t got = data.empty() ? 0 : fread(data.data(), 1, data.size(), f);
     fclose(f);
     data.resize(got);

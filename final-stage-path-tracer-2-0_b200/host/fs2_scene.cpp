@@ -212,6 +212,8 @@ bool Scene::LoadScene(const std::string& filename) {
       Block b = read_block(in);
       std::string mname;
       if (b.word("material", &mname) && mats.count(mname))
+        // the reference casts whatever material the block names (scene.cpp:382-385); the sky is
+        // only ever read through the base-class record, so a non-light material keeps its class
         SetSkyMaterial(std::static_pointer_cast<LightMaterial>(mats[mname]));
     } else if (line.find("quad") != std::string::npos) {
       Block b = read_block(in);

@@ -182,3 +182,19 @@ def test_exr_reader_survives_corrupted_files(tmp_path):
             assert rc in (0, -1, -2)
             if rc == 0:
                 assert got.ndim == 3 and got.shape[2] == 3
+
+
+def test_readers_refuse_a_directory(tmp_path):
+    """fopen() succeeds on a directory and ftell() reports LONG_MAX: the readers must answer
+    'unreadable' instead of sizing a buffer from it (found by fuzzing the .scene parser: a stray
+    carriage return cut a mesh file name down to its directory)."""
+    for ext in (".exr", ".bmp", ".hdr"):
+        d = tmp_path / ("dir" + ext)
+        d.mkdir()
+        rc, _ = _load(str(d))
+        assert rc == -1
+    scene = tmp_path / "s.scene"
+    scene.write_text("material m\n{\n color 1 1 1\n}\nmesh\n{\n file %s/\rgone.obj\n material m\n}\n"
+                     "sphere\n{\n material m\n position 0 0 0\n radius 1\n}\n" % tmp_path)
+    hs = host.HostScene(str(scene))  # the mesh fails to load, the scene still does
+    assert hs.desc().n_objects >= 1
