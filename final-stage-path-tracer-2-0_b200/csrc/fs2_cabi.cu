@@ -52,7 +52,8 @@ struct fs_ctx {
   DeviceBuf nodes, scene_refs, tri_plane, tri_aux, faces, objects, materials, textures, texels,
       lut, lb_nodes, lb_leaf, lb_plane, lb_aux, lb_order;
   DScene ds;
-  uint32_t n_nodes = 0, n_tris = 0, n_faces = 0, n_materials = 0;
+  uint32_t n_nodes = 0, n_tris = 0, n_faces = 0, n_materials = 0, n_objects = 0;
+  float lb_m_floor = 1.0f;  // coordinate scale the leaf-BVH pads were sized for
   // film
   int width = 0, height = 0;
   DeviceBuf sum, aux, mat_id, mean, count, rgb8, scratch, auxpack, post;
@@ -198,6 +199,51 @@ int validate_scene(fs_ctx* ctx, const fs_scene_desc* s) {
     if (n.count == FS_NODE_INTERNAL) {
       if ((uint64_t)n.first + 8 > s->n_nodes)
         return fail(ctx, FS_E_INVALID, "node %u: children out of range", i);
+    }
+  }
+  // Walk every tree once: children must follow their parent (no cycles), no node may be reached
+  // twice, leaf ranges must lie inside the arrays they index, and the depth must fit the
+  // kernels' frame stacks (a deeper subtree would silently read as a miss).
+  {
+    std::vector<uint8_t> seen(s->n_nodes, 0);
+    struct Item {
+      uint32_t node, depth;
+    };
+    std::vector<Item> stack;
+    auto walk = [&](uint32_t root, bool mesh, uint32_t owner) -> int {
+      const uint32_t max_internal_depth = mesh ? FS2_PH_MESH_FRAMES : FS2_PH_SCENE_FRAMES;
+      const uint64_t ref_limit = mesh ? s->n_tris : s->n_scene_refs;
+      stack.clear();
+      stack.push_back(Item{root, 0});
+      while (!stack.empty()) {
+        Item it = stack.back();
+        stack.pop_back();
+        if (seen[it.node])
+          return fail(ctx, FS_E_INVALID, "node %u is reachable twice (%s tree of %u)", it.node,
+                      mesh ? "mesh" : "scene", owner);
+        seen[it.node] = 1;
+        const fs_node& n = s->nodes[it.node];
+        if (n.count == FS_NODE_INTERNAL) {
+          if (it.depth >= max_internal_depth)
+            return fail(ctx, FS_E_INVALID, "%s tree of %u is deeper than %u levels at node %u",
+                        mesh ? "mesh" : "scene", owner, max_internal_depth, it.node);
+          if (n.first <= it.node)
+            return fail(ctx, FS_E_INVALID, "node %u: children (%u) do not follow their parent", it.node,
+                        n.first);
+          for (uint32_t c = 0; c < 8; c++) stack.push_back(Item{n.first + c, it.depth + 1});
+        } else if ((uint64_t)n.first + n.count > ref_limit) {
+          return fail(ctx, FS_E_INVALID, "node %u: leaf range %u+%u exceeds the %llu %s", it.node, n.first,
+                      n.count, (unsigned long long)ref_limit, mesh ? "triangle records" : "scene refs");
+        }
+      }
+      return FS_OK;
+    };
+    int rc;
+    if (s->scene_root >= 0 && (rc = walk((uint32_t)s->scene_root, false, 0))) return rc;
+    for (uint32_t i = 0; i < s->n_objects; i++) {
+      const fs_object& o = s->objects[i];
+      if (o.type == FS_OBJ_MESH && o.u[0] != 0xFFFFFFFFu && o.u[0] < s->n_nodes)
+        if ((rc = walk(o.u[0], true, i))) return rc;
     }
   }
   for (uint32_t i = 0; i < s->n_objects; i++) {
@@ -375,6 +421,60 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   return rc;
 }
 
+// Builds the leaf BVHs of `s` (host threads) and uploads them; the host vectors must outlive the
+// asynchronous copies, hence the synchronisation.
+int upload_lbvh(fs_ctx* ctx, const fs_scene_desc* s, float m_floor_min) {
+  LbvhHost lb;
+  build_lbvh(s, &lb, 9, 0, m_floor_min);
+  int rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_nodes, lb.nodes.data(), lb.nodes.size() * sizeof(LbNode)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_leaf, lb.leaf.data(), lb.leaf.size() * sizeof(LbLeaf)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_plane, lb.plane.data(), lb.plane.size() * 4))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_aux, lb.aux.data(), lb.aux.size() * sizeof(fs_tri_aux)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lb_order, lb.order.data(), lb.order.size() * 4))) return rc;
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  DScene& d = ctx->ds;
+  d.lb_nodes = (const float4*)ctx->lb_nodes.p;
+  d.lb_leaf = (const uint2*)ctx->lb_leaf.p;
+  d.lb_plane = (const float4*)ctx->lb_plane.p;
+  d.lb_aux = (const float4*)ctx->lb_aux.p;
+  d.lb_order = (const uint32_t*)ctx->lb_order.p;
+  d.lb_origin_limit = lb.origin_limit();
+  ctx->lb_m_floor = lb.m_floor;
+  return FS_OK;
+}
+
+// The leaf-BVH box pads bound hit-point rounding for segments that start within
+// DScene::lb_origin_limit of the origin (fs2_lbvh_build.h record_box).  A camera beyond it would
+// send every camera ray down the linear leaf scans, so the leaf BVHs are rebuilt once with pads
+// sized for that camera (rare: the arrays the builder reads are fetched back from the device).
+int ensure_lbvh_for_camera(fs_ctx* ctx, const fs_camera* cam) {
+  float m = 0.f;
+  for (int k = 0; k < 3; k++) m = fmaxf(m, fabsf(cam->origin[k]));
+  m += fabsf(cam->aperture_size);
+  if (!(m > ctx->ds.lb_origin_limit) || !(m <= 1.0e30f) || !ctx->n_tris) return FS_OK;
+  std::vector<fs_node> nodes(ctx->n_nodes);
+  std::vector<float> plane(4 * (size_t)ctx->n_tris);
+  std::vector<fs_tri_aux> aux(ctx->n_tris);
+  std::vector<fs_object> objects(ctx->n_objects);
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  CUDA_TRY(ctx, cudaMemcpy(nodes.data(), ctx->nodes.p, nodes.size() * sizeof(fs_node), cudaMemcpyDeviceToHost));
+  CUDA_TRY(ctx, cudaMemcpy(plane.data(), ctx->tri_plane.p, plane.size() * 4, cudaMemcpyDeviceToHost));
+  CUDA_TRY(ctx, cudaMemcpy(aux.data(), ctx->tri_aux.p, aux.size() * sizeof(fs_tri_aux), cudaMemcpyDeviceToHost));
+  CUDA_TRY(ctx, cudaMemcpy(objects.data(), ctx->objects.p, objects.size() * sizeof(fs_object), cudaMemcpyDeviceToHost));
+  fs_scene_desc d;
+  memset(&d, 0, sizeof d);
+  d.n_nodes = ctx->n_nodes;
+  d.n_tris = ctx->n_tris;
+  d.n_objects = ctx->n_objects;
+  d.nodes = nodes.data();
+  d.tri_plane = plane.data();
+  d.tri_aux = aux.data();
+  d.objects = objects.data();
+  if (ctx->wf_stream) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->wf_stream));
+  return upload_lbvh(ctx, &d, m / 2.0f);  // limit = 3 * m_floor >= 1.5 * |camera|
+}
+
 #include "fs2_build_host.inc"
 
 }  // namespace
@@ -491,22 +591,9 @@ int fs_scene_upload(fs_ctx* ctx, const fs_scene_desc* s) {
   if ((rc = dev_upload(ctx, &ctx->textures, s->textures, (size_t)s->n_textures * sizeof(fs_texture)))) return rc;
   if ((rc = dev_upload(ctx, &ctx->texels, s->texels, (size_t)s->n_texels * 4))) return rc;
   if ((rc = dev_upload(ctx, &ctx->lut, lut4.data(), lut4.size() * 4))) return rc;
-  // leaf BVH over every mesh-tree leaf (fs2_lbvh_build.h); the host vectors must outlive
-  // the asynchronous copies, hence the synchronisation below
-  LbvhHost lb;
-  build_lbvh(s, &lb);
-  if ((rc = dev_upload(ctx, &ctx->lb_nodes, lb.nodes.data(), lb.nodes.size() * sizeof(LbNode)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->lb_leaf, lb.leaf.data(), lb.leaf.size() * sizeof(LbLeaf)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->lb_plane, lb.plane.data(), lb.plane.size() * 4))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->lb_aux, lb.aux.data(), lb.aux.size() * sizeof(fs_tri_aux)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->lb_order, lb.order.data(), lb.order.size() * 4))) return rc;
-  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  // leaf BVH over every mesh-tree leaf (fs2_lbvh_build.h)
+  if ((rc = upload_lbvh(ctx, s, 0.0f))) return rc;
   DScene& d = ctx->ds;
-  d.lb_nodes = (const float4*)ctx->lb_nodes.p;
-  d.lb_leaf = (const uint2*)ctx->lb_leaf.p;
-  d.lb_plane = (const float4*)ctx->lb_plane.p;
-  d.lb_aux = (const float4*)ctx->lb_aux.p;
-  d.lb_order = (const uint32_t*)ctx->lb_order.p;
   d.nodes = (const float4*)ctx->nodes.p;
   d.scene_refs = (const uint32_t*)ctx->scene_refs.p;
   d.tri_plane = (const float4*)ctx->tri_plane.p;
@@ -525,6 +612,7 @@ int fs_scene_upload(fs_ctx* ctx, const fs_scene_desc* s) {
   ctx->n_tris = s->n_tris;
   ctx->n_faces = s->n_faces;
   ctx->n_materials = s->n_materials;
+  ctx->n_objects = s->n_objects;
   ctx->have_scene = true;
   return FS_OK;
 }
@@ -568,6 +656,7 @@ int fs_first_hit(fs_ctx* ctx, const fs_camera* cam, int width, int height, float
   if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_first_hit before fs_scene_upload");
   int rc = set_device(ctx);
   if (rc) return rc;
+  if ((rc = ensure_lbvh_for_camera(ctx, cam))) return rc;
   size_t n = (size_t)width * height;
   if ((rc = dev_alloc(ctx, &ctx->scratch, n * 20))) return rc;
   char* base = (char*)ctx->scratch.p;
@@ -603,6 +692,7 @@ int fs_trace_range(fs_ctx* ctx, const fs_camera* cam, int width, int height, flo
     return fail(ctx, FS_E_INVALID, "fs_trace_range: (%g,%g) outside the image", x, y);
   int rc = set_device(ctx);
   if (rc) return rc;
+  if ((rc = ensure_lbvh_for_camera(ctx, cam))) return rc;
   if ((rc = dev_alloc(ctx, &ctx->scratch, 64))) return rc;
   CamBasis cb = camera_basis(cam, width, height);
   // shift the projection origin so that pixel (0,0) of a 1x1 launch is (x, y)
@@ -648,6 +738,7 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
   if (sample_stride == 0) sample_stride = 1;
   int rc = set_device(ctx);
   if (rc) return rc;
+  if ((rc = ensure_lbvh_for_camera(ctx, cam))) return rc;
   CamBasis cb = camera_basis(cam, ctx->width, ctx->height);
   Film film{(float4*)ctx->sum.p, (float4*)ctx->aux.p, (uint32_t*)ctx->mat_id.p, ctx->width,
             ctx->height};

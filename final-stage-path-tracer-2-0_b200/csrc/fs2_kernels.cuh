@@ -119,8 +119,9 @@ __device__ __forceinline__ void begin_path(const CamBasis& cam, const TraceParam
 // (its radiance is ps.L); otherwise the next segment's ray is in ps.ray.  The aux buffers of
 // the film are written by the last sample of the launch (frame.cpp:78-85: last sample wins).
 __device__ __forceinline__ bool shade_segment(const DScene& S, const CamBasis& cam,
-                                              const Film& film, uint32_t pixel, bool last,
-                                              PathState& ps, const Hit& h, uint32_t& n_shade) {
+                                              const Film& film, const TraceParams& tp,
+                                              uint32_t pixel, bool last, PathState& ps,
+                                              const Hit& h, uint32_t& n_shade) {
   const bool got = h.object != 0xFFFFFFFFu;
   bool done = false;
 
@@ -133,7 +134,9 @@ __device__ __forceinline__ bool shade_segment(const DScene& S, const CamBasis& c
     Mat fm = load_material(S, ps.fog_mat);
     float a = (dist * dist) * fm.density * 0.00005f;
     float threshold = saturate01(0.0f > a ? 0.0f : a);
-    if (ps.rng.uniform() < threshold) {
+    Rng fog_rng = seed_rng(tp.seed ^ FS2_FOG_STREAM_SALT, pixel,
+                           tp.first_sample + ps.s * tp.sample_stride);
+    if (fog_rng.uniform() < threshold) {
       ps.L = fm.diffuse;
       done = true;
     }
@@ -203,7 +206,7 @@ __device__ __forceinline__ bool finish_segment(const DScene& S, const CamBasis& 
                                                const Film& film, const TraceParams& tp,
                                                uint32_t pixel, int px, int py, PathState& ps,
                                                const Hit& h, uint32_t& n_shade) {
-  if (shade_segment(S, cam, film, pixel, ps.s + 1 == tp.n_samples, ps, h, n_shade)) {
+  if (shade_segment(S, cam, film, tp, pixel, ps.s + 1 == tp.n_samples, ps, h, n_shade)) {
     ps.sum = ps.sum + ps.L;
     ps.s++;
     if (ps.s == tp.n_samples) return false;
@@ -357,7 +360,7 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
   for (;;) {
     if (w.st == PH_SEG_START) {  // scene.cpp:227-237
       w.rec = no_hit();
-      w.flags = 0;
+      w.flags = lb_origin_far(S, ps.ray.start) ? PH_F_FAR : 0u;
       w.ssp = 0;
       q = make_lbray(ps.ray);
       if (S.scene_root < 0) {

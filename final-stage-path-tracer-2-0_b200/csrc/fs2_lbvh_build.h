@@ -47,6 +47,8 @@ struct LbvhHost {
   std::vector<LbNode> nodes;
   std::vector<LbLeaf> leaf;        // one per octree node
   std::vector<uint8_t> mesh_leaf;  // 1 for nodes that are leaves of a mesh tree
+  float m_floor = 1.0f;            // scene coordinate scale the record pads were sized for
+  float origin_limit() const { return 3.0f * m_floor; }
 };
 
 namespace lbvh_detail {
@@ -91,33 +93,130 @@ inline void record_vertices(const float pl[4], const fs_tri_aux& a, float v[4][3
   }
 }
 
-// Conservative box of one record: vertex hull padded by 64 ulp of the largest coordinate
-// plus 0.1 % of the extent (rounding of the reference's hit point and barycentrics is a few
-// ulp of the coordinates; the plane-recovered component adds a few more).
-inline Box3 record_box(const float pl[4], const fs_tri_aux& a) {
+// Conservative box of one record: it must contain every point the reference's triangle test
+// (source/math/intersect.cpp:357-419 on the packed constants) can accept, for every segment the
+// walk is used for.  Three sources of slack, each bounded here:
+//
+//  (a) The accepted region is NOT the geometric triangle but {u' >= 0, v' >= 0, u' + v' <= 1}
+//      of the float barycentrics u', v' computed from the stored dot00/01/11 and inv_denom.
+//      For well-shaped triangles the two coincide to rounding; for needles (aspect ratio r) the
+//      stored denominator carries a relative error ~ r^2 * 2^-24, so the region is a scaled /
+//      sheared copy of the triangle, or — beyond r ~ 10^3 — has nothing to do with it.  The
+//      region's corners are therefore solved (in double) from the stored constants themselves,
+//      widened by the evaluation error eta of u', v'; when eta is not small or the linear map
+//      is singular the record gets an unbounded box (it is then tested by every segment that
+//      reaches its leaf: slow, exact).
+//  (b) The hit point p = start + dir * t is rounded: it lies within ~2^-19 (|start| + |p|) of
+//      the exact segment and of the stored plane (the plane residual is bounded by the same
+//      ulp-scale terms, independent of the grazing angle, and is divided by the dominant normal
+//      component: factor <= sqrt 3).  |p| is bounded by the record's own coordinates; |start|
+//      is not known here, so the pad is 2^-17 * max(record magnitude, m_floor) with m_floor the
+//      scene's coordinate scale, and the kernels leave the leaf BVH for the reference's linear
+//      scan whenever |start|_inf > 3 * m_floor (DScene::lb_origin_limit; 4 * 2^-19 = 2^-17).
+//      fs_trace / fs_first_hit rebuild the leaf BVHs with a larger m_floor when the camera itself
+//      lies beyond the limit, so only bounce rays that start on far-away points of unbounded
+//      primitives ever take the linear path.
+//  (c) 0.1 % of the extent on top, which also absorbs the vp = p - p1 rounding.
+inline Box3 record_box(const float pl[4], const fs_tri_aux& a, float m_floor) {
   float v[4][3];
   record_vertices(pl, a, v);
   Box3 b;
   b.reset();
   for (int j = 0; j < 4; j++) b.add(v[j]);
-  float m = 0.f, ext = 0.f;
-  for (int k = 0; k < 3; k++) {
-    m = fmaxf(m, fmaxf(fabsf(b.lo[k]), fabsf(b.hi[k])));
-    ext = fmaxf(ext, b.hi[k] - b.lo[k]);
-  }
-  float pad = m * (64.0f * 1.1920929e-7f) + ext * 1.0e-3f + 1.0e-30f;
-  if (!(pad == pad) || isinf(pad)) {  // degenerate record: make the box cover everything
+  auto everything = [&]() {
     for (int k = 0; k < 3; k++) {
       b.lo[k] = -INFINITY;
       b.hi[k] = INFINITY;
     }
     return b;
+  };
+  // ---- (a) corners of the reference's accepted region, from the stored constants
+  const int drop = (int)(a.face >> 30);
+  const int ia = (drop == 0) ? 1 : 0, ib = (drop == 2) ? 1 : 2;
+  const double inv = a.inv_denom, d00 = a.dot00, d01 = a.dot01, d11 = a.dot11;
+  const double au = (d11 * a.v0a - d01 * a.v1a) * inv, bu = (d11 * a.v0b - d01 * a.v1b) * inv;
+  const double av = (d00 * a.v1a - d01 * a.v0a) * inv, bv = (d00 * a.v1b - d01 * a.v0b) * inv;
+  const double det = au * bv - bu * av;
+  if (!(det == det) || isinf(det) || det == 0.0 || !(inv == inv) || isinf(inv)) {
+    // inv_denom = inf / nan: u', v' are inf / nan wherever they are not exactly 0, so nothing but
+    // a measure-zero set is accepted; a singular map means an unbounded accepted strip
+    if (!(inv == inv) || isinf(inv)) {
+      // keep the vertex hull: harmless and finite
+    } else {
+      return everything();
+    }
+  } else {
+    const double q1x = bv / det, q1y = -av / det;  // (u', v') = (1, 0)
+    const double q2x = -bu / det, q2y = au / det;  // (u', v') = (0, 1)
+    // evaluation error of u' / v' at the far corners (products and sums of the float expression)
+    double eta = 0.0;
+    const double qs[2][2] = {{q1x, q1y}, {q2x, q2y}};
+    for (int c = 0; c < 2; c++) {
+      const double x = fabs(qs[c][0]), y = fabs(qs[c][1]);
+      const double m02 = fabs((double)a.v0a) * x + fabs((double)a.v0b) * y;
+      const double m12 = fabs((double)a.v1a) * x + fabs((double)a.v1b) * y;
+      const double eu = (fabs(d11) * m02 + fabs(d01) * m12) * fabs(inv);
+      const double ev = (fabs(d00) * m12 + fabs(d01) * m02) * fabs(inv);
+      eta = fmax(eta, fmax(eu, ev));
+    }
+    eta *= 4.76837158203125e-07;  // 2^-21
+    if (!(eta == eta) || eta > 0.125) return everything();
+    const double e = 2.0 * eta;
+    const double uv[3][2] = {{-e, -e}, {1.0 + 3.0 * e, -e}, {-e, 1.0 + 3.0 * e}};
+    const double nd = pl[drop];
+    for (int c = 0; c < 3; c++) {
+      float p[3];
+      const double x = uv[c][0] * q1x + uv[c][1] * q2x, y = uv[c][0] * q1y + uv[c][1] * q2y;
+      p[ia] = (float)((double)a.p1[ia] + x);
+      p[ib] = (float)((double)a.p1[ib] + y);
+      p[drop] = a.p1[drop];
+      if (nd != 0.0) p[drop] = (float)(-((double)pl[3] + (double)pl[ia] * p[ia] + (double)pl[ib] * p[ib]) / nd);
+      for (int k = 0; k < 3; k++)
+        if (!(p[k] == p[k]) || isinf(p[k])) return everything();
+      b.add(p);
+    }
   }
+  // ---- (b), (c)
+  float m = m_floor, ext = 0.f;
+  for (int k = 0; k < 3; k++) {
+    m = fmaxf(m, fmaxf(fabsf(b.lo[k]), fabsf(b.hi[k])));
+    ext = fmaxf(ext, b.hi[k] - b.lo[k]);
+  }
+  float pad = m * 7.62939453125e-06f /* 2^-17 */ + ext * 1.0e-3f + 1.0e-30f;
+  if (!(pad == pad) || isinf(pad)) return everything();
   for (int k = 0; k < 3; k++) {
     b.lo[k] -= pad;
     b.hi[k] += pad;
   }
   return b;
+}
+
+// Coordinate scale of the scene: the largest finite |coordinate| of any bounded object's bounds
+// or mesh-tree root box (at least 1; PlanarObject's synthetic +-1000 box is skipped).  Ray
+// origins — the camera, or points on objects — are expected within a few multiples of it;
+// DScene::lb_origin_limit = 3 * m_floor.
+inline float scene_coordinate_scale(const fs_scene_desc* s) {
+  float m = 1.0f;
+  auto take = [&](float c) {
+    c = fabsf(c);
+    if (c == c && c <= 1.0e6f && c > m) m = c;
+  };
+  for (uint32_t o = 0; o < s->n_objects; o++) {
+    const fs_object& ob = s->objects[o];
+    if (ob.type == FS_OBJ_PLANE) continue;
+    for (int k = 0; k < 3; k++) {
+      take(ob.bmin[k]);
+      take(ob.bmax[k]);
+    }
+    if (ob.type == FS_OBJ_MESH && ob.u[0] < s->n_nodes) {
+      const fs_node& nd = s->nodes[ob.u[0]];
+      for (int k = 0; k < 3; k++) {
+        take(nd.bmin[k]);
+        take(nd.bmax[k]);
+      }
+    }
+  }
+  return m;
 }
 
 inline uint32_t spread3(uint32_t x) {
@@ -153,7 +252,7 @@ inline uint32_t leaf_node_count(uint32_t n) {
 
 // Builds one leaf: permutes records [first, first+count) and writes its nodes, root first,
 // then level by level towards the quad level (children of a node are contiguous).
-inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out) {
+inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out, float m_floor) {
   const uint32_t n = job.count, first = job.first;
   std::vector<Box3> boxes(n);
   std::vector<uint64_t> keys(n);
@@ -162,7 +261,7 @@ inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out
   std::vector<float> cen(3 * (size_t)n);
   for (uint32_t i = 0; i < n; i++) {
     const float* pl = s->tri_plane + 4 * (size_t)(first + i);
-    boxes[i] = record_box(pl, s->tri_aux[first + i]);
+    boxes[i] = record_box(pl, s->tri_aux[first + i], m_floor);
     for (int k = 0; k < 3; k++) {
       float c = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
       if (!(c == c) || isinf(c)) c = 0.f;
@@ -257,8 +356,10 @@ inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out
 
 // Builds the leaf BVHs of every mesh-tree leaf of `s`.  min_leaf: leaves with fewer records
 // keep root = 0xFFFFFFFF (scanned linearly).  Leaves beyond the level cap stay linear too.
+// m_floor_min: lower bound for the coordinate scale the pads are sized for (the camera's distance
+// from the origin when it lies outside the scene's own scale).
 inline void build_lbvh(const fs_scene_desc* s, LbvhHost* out, uint32_t min_leaf = 9,
-                       unsigned threads = 0) {
+                       unsigned threads = 0, float m_floor_min = 0.0f) {
   using namespace lbvh_detail;
   out->plane.assign(s->tri_plane, s->tri_plane + 4 * (size_t)s->n_tris);
   out->aux.assign(s->tri_aux, s->tri_aux + s->n_tris);
@@ -300,6 +401,7 @@ inline void build_lbvh(const fs_scene_desc* s, LbvhHost* out, uint32_t min_leaf 
     }
   }
   out->nodes.resize(total_nodes ? total_nodes : 1);
+  const float m_floor = out->m_floor = fmaxf(scene_coordinate_scale(s), m_floor_min);
   for (const LeafJob& j : jobs) out->leaf[j.node].root = j.node_base;
   if (threads == 0) threads = std::thread::hardware_concurrency();
   if (threads == 0) threads = 1;
@@ -309,7 +411,7 @@ inline void build_lbvh(const fs_scene_desc* s, LbvhHost* out, uint32_t min_leaf 
     for (;;) {
       size_t i = next.fetch_add(1);
       if (i >= jobs.size()) break;
-      build_leaf(s, jobs[i], out);
+      build_leaf(s, jobs[i], out, m_floor);
     }
   };
   if (threads <= 1 || jobs.size() < 8) {

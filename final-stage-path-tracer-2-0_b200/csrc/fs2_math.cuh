@@ -77,10 +77,22 @@ __device__ __forceinline__ V3 refract(V3 v, V3 n, float index) {
   return normalize(r);
 }
 
+// sin / cos of a float angle, correctly rounded for all practical purposes: evaluated in double
+// (<= 2 ulp of a double) and rounded once.  The reference calls the host libm's float versions
+// (engine.cpp:235-236, vector3.h:317-318), which are correctly rounded but for rare cases, so
+// path-by-path comparison against the CPU oracle sees the same bits; CUDA's sincosf (2 ulp) does
+// not.
+__device__ __forceinline__ void sincos_rn(float angle, float& s, float& c) {
+  double ds, dc;
+  sincos((double)angle, &ds, &dc);
+  s = (float)ds;
+  c = (float)dc;
+}
+
 // reference source/math/vector3.h:315-333 (axis is used as given, not normalised)
 __device__ __forceinline__ V3 rotate_axis(V3 p, float angle, V3 a) {
   float s, c;
-  sincosf(angle, &s, &c);
+  sincos_rn(angle, s, c);
   float k = 1.0f - c;
   V3 o;
   o.x = (c + k * a.x * a.x) * p.x;

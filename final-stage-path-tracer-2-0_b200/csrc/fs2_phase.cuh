@@ -81,6 +81,7 @@ struct PhLane {
 #define PH_F_RET 2u
 #define PH_F_SIMPROVED 4u
 #define PH_F_FOUND 8u
+#define PH_F_FAR 16u  // segment starts beyond DScene::lb_origin_limit: linear mesh-leaf scans
 
 // ---- shared-memory columns
 struct PhSmem {
@@ -107,7 +108,7 @@ struct PhSmem {
 template <bool TREE = true>
 __device__ __forceinline__ LbRay ph_segment_start(const DScene& S, PhLane& w, const Ray& r) {
   w.rec = no_hit();
-  w.flags = 0;
+  w.flags = lb_origin_far(S, r.start) ? PH_F_FAR : 0u;
   w.ssp = 0;
   if (!TREE || S.scene_root < 0) {
     w.obj_i = 0;
@@ -152,8 +153,9 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
     } else {
       // mesh leaf (mesh.cpp:86-111)
       uint32_t root = __ldg(&S.lb_leaf[w.cur].x);
-      if (r.zero_length || (root == 0xFFFFFFFFu && n.count > 16u)) {
-        // rare: point query / leaf beyond the BVH level cap -> linear scan in reference order
+      if (r.zero_length || (w.flags & PH_F_FAR) || (root == 0xFFFFFFFFu && n.count > 16u)) {
+        // rare: point query / far-away origin / leaf beyond the BVH level cap -> linear scan in
+        // reference order
         ColdResult cr = mesh_leaf_cold<STATS>(S, n.first, n.count, r, w.cur_obj, w.rec, c);
         w.rec = cr.h;
         c = cr.c;

@@ -47,6 +47,12 @@ __device__ __forceinline__ Rng seed_rng(uint64_t seed, uint32_t pixel, uint32_t 
   return r;
 }
 
+// Stream of the depth-0 fog decision (material.cpp:330-337).  The reference's recursion draws it
+// after the whole sub-path has returned; a forward path needs it at the next hit, so it comes
+// from a stream of its own (same hash, salted seed) and the order of the path's other draws
+// stays the reference's.
+#define FS2_FOG_STREAM_SALT 0xF06F06F06F06F06Full
+
 // ------------------------------------------------------------------ camera
 // Per-frame camera basis, computed on the host exactly as reference
 // source/engine.cpp:170-197 / :300-313 does (tanf/atan/tan of the host libm).
@@ -78,7 +84,7 @@ __device__ __forceinline__ void apply_dof(const CamBasis& b, Rng& rng, Ray& r) {
   float angle = (float)((double)rng.uniform() * 2.0 * (double)FS2_PI);
   float mag = approx_sqrt(rng.uniform()) * b.aperture;
   float sn, cs;
-  sincosf(angle, &sn, &cs);
+  sincos_rn(angle, sn, cs);
   V3 off = ld3(b.right) * cs * mag + ld3(b.up) * sn * mag;
   V3 start = r.start + off;
   V3 stop = start + normalize(focal - start) * b.z_far;
@@ -155,10 +161,14 @@ __device__ __forceinline__ V3 random_refraction(const DScene& S, Rng& rng, V3 in
   return rotate_axis(refl, delta, axis);
 }
 
-// x^50 by squaring (reference material.cpp:280 uses double pow; parity is statistical)
-__device__ __forceinline__ float pow50(float x) {
-  float x2 = x * x, x4 = x2 * x2, x8 = x4 * x4, x16 = x8 * x8, x32 = x16 * x16;
-  return x32 * x16 * x2;
+// float32 dot_spec = pow(half_vec.dot(n), 50) — reference material.cpp:280 promotes to double
+// pow and rounds the result to float.  x^50 by squaring in double (7 products, <= 4 ulp of a
+// double) rounds to the same float as a correctly rounded pow except when the exact value lies
+// within 2^-50 of a float rounding boundary.
+__device__ __forceinline__ float pow50(float xf) {
+  double x = (double)xf;
+  double x2 = x * x, x4 = x2 * x2, x8 = x4 * x4, x16 = x8 * x8, x32 = x16 * x16;
+  return (float)(x32 * x16 * x2);
 }
 
 // Outcome of one surface interaction in forward form.

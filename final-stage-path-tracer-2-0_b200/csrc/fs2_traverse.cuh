@@ -34,7 +34,15 @@ struct DScene {
   uint32_t n_lut;
   uint32_t sky_material;
   int32_t scene_root;
+  // segments that start farther than this from the origin (max-norm) scan mesh leaves linearly:
+  // the leaf BVH's box pads bound the rounding of hit points only up to that distance
+  // (fs2_lbvh_build.h record_box (b))
+  float lb_origin_limit;
 };
+
+__device__ __forceinline__ bool lb_origin_far(const DScene& S, V3 s) {
+  return !(fmaxf(fmaxf(fabsf(s.x), fabsf(s.y)), fabsf(s.z)) <= S.lb_origin_limit);
+}
 
 struct Counters {
   uint32_t n_node, n_tri, n_bary, n_prim;  // reference-equivalent work
@@ -402,6 +410,7 @@ __device__ __forceinline__ bool primitive_trace(const DScene& S, uint32_t oi, ui
 struct LbCtx {
   LbRay q;
   uint2* stack;  // this lane's column of the shared-memory stack
+  bool far;      // lb_origin_far(ray start): linear leaf scans for this segment
 };
 
 template <bool STATS, bool LB = false>
@@ -414,7 +423,7 @@ __device__ __forceinline__ bool object_trace(const DScene& S, uint32_t oi, const
     if (root == 0xFFFFFFFFu) return false;
     return walk_octree<FS2_MESH_STACK, STATS>(
         S, root, r, h, c, [&](uint32_t node, uint32_t first, uint32_t count, Hit& best) {
-          if (LB && !r.zero_length)
+          if (LB && !r.zero_length && !lb->far)
             return lbvh_leaf<STATS>(S, node, first, count, r, lb->q, oi, best, c, lb->stack);
           return mesh_leaf<STATS>(S, first, count, r, oi, best, c);
         });
@@ -518,6 +527,7 @@ __device__ __forceinline__ Hit scene_trace(const DScene& S, const Ray& r, Counte
   if (LB) {
     lbc.q = make_lbray(r);
     lbc.stack = lb_stack;
+    lbc.far = lb_origin_far(S, r.start);
   }
   const LbCtx* lb = LB ? &lbc : nullptr;
   if (S.scene_root < 0) {

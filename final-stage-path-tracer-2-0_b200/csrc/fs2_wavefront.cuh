@@ -325,7 +325,7 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
     int px, py;
     wf_slot_pixel(B, pixslot, px, py);
     const uint32_t pixel = (uint32_t)(py * film.width + px);
-    if (shade_segment(S, cam, film, pixel, ps.s + 1 == tp.n_samples, ps, h, n_shade)) {
+    if (shade_segment(S, cam, film, tp, pixel, ps.s + 1 == tp.n_samples, ps, h, n_shade)) {
       atomicAdd(film.sum + pixel, make_float4(ps.L.x, ps.L.y, ps.L.z, 1.0f));
       finished = 1;
       need = true;

@@ -112,6 +112,32 @@ def trace_scene(scene, cam, w, h, frames, bands, seeds=None, aux=True):
     return film
 
 
+FOG_SHARED_STREAM = 1 << 30
+
+
+def trace_paths(scene, cam, w, h, n_samples, first_sample=0, stride=1, seed=1, flags=0):
+    """Per-path records with the device's random streams (oracle RngMode kDevice): arrays of
+    shape [n_samples, h*w(, 3)] — rgb, ray_count, normal, depth, mat_id — plus counters."""
+    n = w * h
+    out = {"rgb": np.zeros((n_samples, n, 3), np.float32),
+           "ray_count": np.zeros((n_samples, n), np.uint32),
+           "normal": np.zeros((n_samples, n, 3), np.float32),
+           "depth": np.zeros((n_samples, n), np.float32),
+           "mat_id": np.zeros((n_samples, n), np.uint64)}
+    counters = np.zeros(6, np.uint64)
+    d = scene.desc()
+    rc = lib().fs2o_trace_paths(C.byref(d), C.byref(cam), w, h, C.c_uint32(first_sample),
+                                C.c_uint32(n_samples), C.c_uint32(stride), C.c_uint64(seed),
+                                C.c_int(flags), _p(out["rgb"]), _p(out["ray_count"]),
+                                _p(out["normal"]), _p(out["depth"]), _p(out["mat_id"]),
+                                _p(counters))
+    if rc != 0:
+        raise RuntimeError("fs2o_trace_paths failed: %d" % rc)
+    out["counters"] = dict(zip(["n_segments", "n_node", "n_tri", "n_bary", "n_prim", "n_shade"],
+                               [int(c) for c in counters]))
+    return out
+
+
 # ------------------------------------------------------------------ compiled reference
 def have_ref():
     return os.path.exists(REF_BIN) and os.access(REF_BIN, os.X_OK)

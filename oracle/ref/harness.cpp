@@ -36,6 +36,9 @@
 #include "fs2_blob.h"
 #include "fs2_cabi.h"
 #include "fs2_pack.h"
+#ifdef FS2_REF_CTR
+#include "ctr_rng.h"
+#endif
 
 // ---------------------------------------------------------------- interposers
 static bool g_fake_clock = true;
@@ -439,6 +442,38 @@ static int render(Scene* scene, const Camera& cam, uint32_t W, uint32_t H, uint3
   return 0;
 }
 
+#ifdef FS2_REF_CTR
+// ---------------------------------------------------------------- per-path dump
+// fs2_ref_ctr only: `samples` TraceScene calls of the unmodified reference with one worker
+// thread, every path drawing from the device's stream of (seed, pixel, sample index)
+// (ctr_rng.cpp).  File: u32 magic "F2PT", W, H, samples, then [samples][H*W] PathRecord.
+static int dump_paths(Scene* scene, const Camera& cam, uint32_t W, uint32_t H, uint32_t samples,
+                      uint32_t first_sample, uint32_t stride, uint64_t seed, const char* path) {
+  DisplayFrame frame(W, H);
+  std::vector<fs2ctr::PathRecord> out((size_t)samples * W * H);
+  memset(out.data(), 0, out.size() * sizeof(fs2ctr::PathRecord));
+  g_threads = 1;
+  fs2ctr::g.seed = seed;
+  fs2ctr::g.out = out.data();
+  fs2ctr::g.active = true;
+  for (uint32_t k = 0; k < samples; k++) {
+    fs2ctr::g.sample = first_sample + k * stride;
+    fs2ctr::g.sample_slot = k;
+    TraceScene(cam, scene, &frame);
+  }
+  fs2ctr::g.active = false;
+  FILE* f = fopen(path, "wb");
+  if (!f) return 1;
+  uint32_t hdr[4] = {0x54503246u /* "F2PT" */, W, H, samples};
+  fwrite(hdr, sizeof hdr, 1, f);
+  fwrite(out.data(), sizeof(fs2ctr::PathRecord), out.size(), f);
+  fclose(f);
+  printf("FS2REF paths %ux%u x %u samples written to %s; scan-order errors: %llu\n", W, H, samples,
+         path, (unsigned long long)fs2ctr::g.order_errors);
+  return fs2ctr::g.order_errors ? 2 : 0;
+}
+#endif
+
 // ---------------------------------------------------------------- built-in API scene
 // Objects and materials the .scene grammar cannot express: PlanarObject,
 // DiscObject, FogMaterial, GlowMaterial, textured Metal — built through the reference's
@@ -482,7 +517,8 @@ static void usage() {
   fprintf(stderr,
           "usage: fs2_ref SCENE [--width W] [--height H] [--flatten out.fs2]\n"
           "               [--firsthit out.bin] [--render out.bin] [--frames N] [--threads T]\n"
-          "               [--clock0 MS | --realclock] [--aperture A] [--focal F] [--json out.json]\n");
+          "               [--clock0 MS | --realclock] [--aperture A] [--focal F] [--json out.json] [--fast]\n"
+          "       fs2_ref_ctr only: [--paths out.bin --samples K --first-sample F --stride T --seed S]\n");
 }
 
 int main(int argc, char** argv) {
@@ -494,8 +530,11 @@ int main(int argc, char** argv) {
   uint32_t W = 64, H = 64, frames = 1;
   const char *flatten_path = nullptr, *firsthit_path = nullptr, *render_path = nullptr,
              *json_path = nullptr;
-  bool do_render = false, have_aperture = false, have_focal = false;
+  bool do_render = false, have_aperture = false, have_focal = false, fast = false;
   float aperture = 0, focal = 0;
+  const char* paths_path = nullptr;
+  uint32_t path_samples = 1, path_first = 0, path_stride = 1;
+  uint64_t path_seed = 1;
   for (int i = 2; i < argc; i++) {
     std::string a = argv[i];
     auto next = [&]() -> const char* { return (i + 1 < argc) ? argv[++i] : ""; };
@@ -512,6 +551,12 @@ int main(int argc, char** argv) {
     else if (a == "--aperture") { aperture = (float)atof(next()); have_aperture = true; }
     else if (a == "--focal") { focal = (float)atof(next()); have_focal = true; }
     else if (a == "--json") json_path = next();
+    else if (a == "--fast") fast = true;  // Camera::fast_render_enabled (engine.cpp:68-70)
+    else if (a == "--paths") paths_path = next();
+    else if (a == "--samples") path_samples = (uint32_t)atoi(next());
+    else if (a == "--first-sample") path_first = (uint32_t)atoi(next());
+    else if (a == "--stride") path_stride = (uint32_t)atoi(next());
+    else if (a == "--seed") path_seed = strtoull(next(), nullptr, 10);
     else { usage(); return 64; }
   }
   if (g_threads == 0) g_threads = 1;
@@ -532,6 +577,7 @@ int main(int argc, char** argv) {
   if (scene.GetCameraCount() > 0) cam = *scene.GetCamera(0);
   if (have_aperture) cam.aperture_size = aperture;
   if (have_focal) cam.focal_depth = focal;
+  if (fast) cam.fast_render_enabled = true;
 
   int rc = 0;
   if (flatten_path) {
@@ -562,5 +608,13 @@ int main(int argc, char** argv) {
   }
   if (firsthit_path) rc |= dump_first_hit(&scene, cam, W, H, firsthit_path);
   if (do_render) rc |= render(&scene, cam, W, H, frames, render_path, json_path);
+  if (paths_path) {
+#ifdef FS2_REF_CTR
+    rc |= dump_paths(&scene, cam, W, H, path_samples, path_first, path_stride, path_seed, paths_path);
+#else
+    fprintf(stderr, "--paths needs fs2_ref_ctr (the binary linked with ctr_rng.cpp)\n");
+    return 64;
+#endif
+  }
   return rc;
 }

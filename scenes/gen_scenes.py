@@ -362,6 +362,146 @@ def scene_grid(outdir, nx, nz, name, aperture=1.5):
     return s
 
 
+# ----------------------------------------------------------------- adversarial meshes
+# Fixtures aimed at the leaf BVH's exactness argument (csrc/fs2_lbvh_build.h record_box): the
+# reference's linear leaf loop and the BVH walk must agree where float geometry is at its worst.
+def _write_obj(path, verts, faces, comment):
+    with open(path, "w") as f:
+        f.write("# fs2-b200 %s\n" % comment)
+        f.write("".join("v %.9g %.9g %.9g\n" % tuple(v) for v in verts))
+        f.write("".join("f %d %d %d\n" % tuple(t) for t in faces))
+    return len(faces)
+
+
+def needles_obj(path, n=2400, seed=21):
+    """Sliver triangles with aspect ratios 10 ... 10^5 (their stored barycentric denominators
+    lose most or all of their bits), mixed with ordinary ones, in a +-12 cube."""
+    rng = np.random.RandomState(seed)
+    verts, faces = [], []
+    for k in range(n):
+        base = rng.uniform(-12, 12, 3)
+        d = rng.normal(size=3)
+        d /= np.linalg.norm(d)
+        length = rng.uniform(4.0, 18.0)
+        side = np.cross(d, rng.normal(size=3))
+        side /= np.linalg.norm(side)
+        aspect = [1.5, 10.0, 100.0, 1.0e3, 1.0e4, 1.0e5][k % 6]
+        a = base
+        b = base + d * length
+        c = base + d * length * rng.uniform(0.2, 0.8) + side * (length / aspect)
+        i = len(verts)
+        verts += [a, b, c]
+        faces.append((i + 1, i + 2, i + 3))
+    return _write_obj(path, verts, faces, "needle triangles n=%d seed=%d" % (n, seed))
+
+
+def _small_sphere(nu, nv):
+    """Unit sphere as (verts [n,3], faces [m,3] 1-based); 2*nu*(nv-1) triangles."""
+    verts = []
+    for j in range(nv + 1):
+        th = math.pi * j / nv
+        for i in range(nu):
+            ph = 2 * math.pi * i / nu
+            verts.append((math.sin(th) * math.cos(ph), math.cos(th), math.sin(th) * math.sin(ph)))
+    faces = []
+    for j in range(nv):
+        for i in range(nu):
+            a = j * nu + i
+            b = j * nu + (i + 1) % nu
+            c = a + nu
+            d = b + nu
+            if j > 0:
+                faces.append((a + 1, b + 1, c + 1))
+            if j < nv - 1:
+                faces.append((b + 1, d + 1, c + 1))
+    return np.array(verts), np.array(faces)
+
+
+def wide_range_obj(path):
+    """One mesh whose coordinates span 10^-3 ... 5*10^3: seven spheres of radius 10^-3 ... 10^3
+    fanned out around the origin, each four radii away (so all are about equally large on
+    screen), plus two ground triangles 8 000 units across."""
+    sv, sf = _small_sphere(16, 9)
+    verts, faces = [], []
+    for k in range(7):
+        r = 10.0 ** (k - 3)
+        ang = math.radians(-36 + 12 * k)
+        c = np.array([4.0 * r * math.sin(ang), 0.15 * r * (k - 3), 4.0 * r * math.cos(ang)])
+        base = len(verts)
+        verts += list(sv * r + c)
+        faces += [tuple(int(i) + base for i in t) for t in sf]
+    base = len(verts)
+    verts += [np.array(v) for v in ((-4000.0, -1200.0, -100.0), (4000.0, -1200.0, -100.0),
+                                    (4000.0, -1100.0, 4900.0), (-4000.0, -1100.0, 4900.0))]
+    faces += [(base + 1, base + 3, base + 2), (base + 1, base + 4, base + 3)]
+    return _write_obj(path, verts, faces, "wide coordinate range")
+
+
+def scene_needles(outdir):
+    obj = os.path.join(outdir, "needles.obj")
+    if not os.path.exists(obj):
+        needles_obj(obj)
+    s = "# fs2-b200 adversarial: needle triangles\n"
+    s += common_materials(outdir, textured_floor=False)
+    s += block("sky", material="sky_mat")
+    s += camera(position=(-6.0, 9.0, -44.0), target=(0.0, 1.0, 0.0))
+    s += block("sphere", material="lamp_mat", position=(-10.0, 40.0, -20.0), radius=6.0)
+    s += block("mesh", file=obj, material="red_diffuse", translation=(0.0, 2.0, 0.0),
+               scale=(1.0, 1.0, 1.0), rotation=(0.0, 1.0, 0.0, 0.3))
+    return s
+
+
+def scene_far_mesh(outdir):
+    """The config-2 layout moved to (9000, 9000, 9000): one ulp is ~10^-3 there."""
+    obj = os.path.join(outdir, "far_sphere_48x25.obj")
+    if not os.path.exists(obj):
+        uv_sphere_obj(obj, 48, 25)
+    o = 9000.0
+    s = "# fs2-b200 adversarial: mesh far from the origin\n"
+    s += common_materials(outdir, textured_floor=False)
+    s += block("sky", material="sky_mat")
+    s += camera(position=(o - 4.0, o + 11.0, o - 46.0), target=(o, o + 7.0, o))
+    s += block("quad", material="floor_mat", position=(o, o, o), normal=(0.02, 1.0, 0.01),
+               width=200.0, height=200.0)
+    s += block("sphere", material="lamp_mat", position=(o - 10.0, o + 40.0, o - 20.0), radius=6.0)
+    s += block("mesh", file=obj, material="gold_metal", translation=(o - 9.0, o + 7.0, o + 2.0),
+               scale=(6.0, 6.0, 6.0), rotation=(0.0, 1.0, 0.0, 0.4))
+    s += block("mesh", file=obj, material="mirror_mat", translation=(o + 9.0, o + 7.0, o + 4.0),
+               scale=(6.0, 6.0, 6.0), rotation=(0.0, 0.0, 1.0, 0.7))
+    return s
+
+
+def scene_far_camera(outdir):
+    """A unit-sized mesh at the origin seen from 500 units away: the camera lies far outside the
+    scene's own coordinate scale (the leaf-BVH pads are re-sized for it, fs2_cabi.cu)."""
+    obj = os.path.join(outdir, "far_sphere_48x25.obj")
+    if not os.path.exists(obj):
+        uv_sphere_obj(obj, 48, 25)
+    s = "# fs2-b200 adversarial: camera far outside the scene scale\n"
+    s += common_materials(outdir, textured_floor=False)
+    s += block("sky", material="sky_mat")
+    s += camera(position=(-300.0, 60.0, -400.0), target=(0.0, 0.0, 0.0), fov=0.6)
+    s += block("sphere", material="lamp_mat", position=(-1.0, 4.0, -2.0), radius=0.6)
+    s += block("mesh", file=obj, material="green_ceramic", translation=(0.0, 0.0, 0.0),
+               scale=(1.0, 1.0, 1.0), rotation=(0.0, 1.0, 0.0, 0.0))
+    s += block("mesh", file=obj, material="mirror_mat", translation=(2.2, 0.2, 0.5),
+               scale=(0.8, 0.8, 0.8), rotation=(1.0, 0.0, 0.0, 0.5))
+    return s
+
+
+def scene_wide_range(outdir):
+    obj = os.path.join(outdir, "wide_range.obj")
+    if not os.path.exists(obj):
+        wide_range_obj(obj)
+    s = "# fs2-b200 adversarial: coordinates spanning 1e-3 ... 5e3 in one mesh\n"
+    s += common_materials(outdir, textured_floor=False)
+    s += block("sky", material="sky_mat")
+    s += camera(position=(0.0, 0.0, 0.0), target=(0.0, -0.05, 1.0), fov=80.0)
+    s += block("mesh", file=obj, material="green_ceramic", translation=(0.0, 0.0, 0.0),
+               scale=(1.0, 1.0, 1.0), rotation=(0.0, 1.0, 0.0, 0.0))
+    return s
+
+
 def scene_random(outdir, seed):
     """Seeded random scene for the fuzz parity test: random camera (inside the cloud for odd
     seeds), spheres / rotated cuboids / tilted quads of every material, one or two small
@@ -428,6 +568,10 @@ SCENES = {
     "grid_tiny": lambda d: scene_grid(d, 24, 12, "gtiny", aperture=0.0),
     "grid_small": lambda d: scene_grid(d, 64, 32, "gsmall"),
     "grid4m": lambda d: scene_grid(d, 2048, 1024, "g4m"),
+    "needles": scene_needles,
+    "far_mesh": scene_far_mesh,
+    "far_camera": scene_far_camera,
+    "wide_range": scene_wide_range,
 }
 
 

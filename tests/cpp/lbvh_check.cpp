@@ -227,7 +227,10 @@ int main(int argc, char** argv) {
     printf("ok 0 0 (no mesh leaves)\n");
     return 0;
   }
-  uint64_t queries = 0, mismatches = 0, hits = 0, n_nodes = 0, n_tests = 0, n_linear = 0;
+  // segments that start beyond origin_limit never reach the walk (the kernels scan such leaves
+  // linearly, fs2_phase.cuh PH_F_FAR); origins up to the limit must be exact
+  const float origin_limit = lb.origin_limit();
+  uint64_t queries = 0, mismatches = 0, hits = 0, n_nodes = 0, n_tests = 0, n_linear = 0, n_far = 0;
   int max_sp = 0;
   for (int r = 0; r < n_rays; r++) {
     float s[3], e[3], d[3];
@@ -237,6 +240,17 @@ int main(int argc, char** argv) {
       // origins inside and well outside the meshes; targets inside the mesh bounds
       s[k] = lo[k] + ext * (float)(mode == 0 ? rnd() : (rnd() * 5.0 - 2.0));
       e[k] = lo[k] + ext * (float)rnd();
+    }
+    if (r % 7 == 6) {
+      // origin on the surface of the cube |s|_inf = origin_limit: the worst rounding of the hit
+      // point the box pads have to cover
+      int ax = (int)(rnd() * 3) % 3;
+      for (int k = 0; k < 3; k++) s[k] = origin_limit * (float)(rnd() * 2.0 - 1.0);
+      s[ax] = (rnd() < 0.5 ? -origin_limit : origin_limit);
+    }
+    if (fmaxf(fmaxf(fabsf(s[0]), fabsf(s[1])), fabsf(s[2])) > origin_limit) {
+      n_far++;
+      continue;
     }
     if (mode == 3) e[r % 3] = s[r % 3];  // axis-parallel component
     if (r % 5 == 4) {
@@ -276,10 +290,10 @@ int main(int argc, char** argv) {
     }
   }
   printf("%s %llu queries, %llu hits, %llu mismatches; per query: %.1f linear tests vs %.1f nodes + %.1f tests; "
-         "max stack %d\n",
+         "max stack %d; origin limit %g (%llu segments beyond it skipped)\n",
          mismatches ? "FAIL" : "ok", (unsigned long long)queries, (unsigned long long)hits,
          (unsigned long long)mismatches, (double)n_linear / queries, (double)n_nodes / queries,
-         (double)n_tests / queries, max_sp);
+         (double)n_tests / queries, max_sp, origin_limit, (unsigned long long)n_far);
   free(storage);
   return mismatches ? 1 : 0;
 }

@@ -9,7 +9,11 @@ import fs2_b200  # noqa: F401
 from fs2_b200 import abi
 
 GOLDEN_DIR = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
-GOLDEN_SCENES = ["api", "demo", "demo_dof", "many303", "mesh_tiny", "glass_small", "grid_tiny"]
+GOLDEN_SCENES = ["api", "demo", "demo_dof", "many303", "mesh_tiny", "glass_small", "grid_tiny",
+                 # adversarial meshes for the leaf BVH (scenes/gen_scenes.py): sliver triangles, a mesh
+                 # at (9000, 9000, 9000), a camera 500 units from a unit-sized scene, coordinates
+                 # spanning 1e-3 ... 5e3 in one mesh
+                 "needles", "far_mesh", "far_camera", "wide_range"]
 
 
 class Golden:
@@ -28,6 +32,17 @@ class Golden:
         self.film = {k[5:]: z[k] for k in z.files if k.startswith("film_")}
 
 
+class GoldenPaths:
+    """tests/golden/paths_NAME.npz: per-path TraceResults of the unmodified reference fed the
+    CUDA path's random streams (oracle/_ref/fs2_ref_ctr), [samples, h*w] each."""
+
+    def __init__(self, name):
+        z = np.load(os.path.join(GOLDEN_DIR, "paths_" + name + ".npz"))
+        self.w, self.h, self.samples, self.seed = (int(v) for v in z["meta"])
+        for k in ("rgb", "ray_count", "normal", "depth", "mat_id", "fast_rgb", "fast_ray_count"):
+            setattr(self, k, z[k])
+
+
 _cache = {}
 
 
@@ -35,6 +50,27 @@ def golden(name):
     if name not in _cache:
         _cache[name] = Golden(name)
     return _cache[name]
+
+
+def golden_paths(name):
+    key = "paths_" + name
+    if key not in _cache:
+        _cache[key] = GoldenPaths(name)
+    return _cache[key]
+
+
+def ulp_distance(a, b):
+    """Distance in units in the last place between two float32 arrays (same shape), treating
+    +0 / -0 as equal; nan vs anything = huge."""
+    a = np.ascontiguousarray(a, np.float32)
+    b = np.ascontiguousarray(b, np.float32)
+    ia = a.view(np.int32).astype(np.int64)
+    ib = b.view(np.int32).astype(np.int64)
+    ia = np.where(ia < 0, -(ia & 0x7FFFFFFF), ia)
+    ib = np.where(ib < 0, -(ib & 0x7FFFFFFF), ib)
+    d = np.abs(ia - ib)
+    d[np.isnan(a) | np.isnan(b)] = 1 << 40
+    return d
 
 
 def bits(a):

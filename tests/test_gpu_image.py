@@ -1,8 +1,17 @@
 """Converged-image parity of the CUDA path tracer (fs_trace) with the CPU oracle, which is
-bit-exact with the reference renderer (tests/test_oracle_golden.py).  Random streams differ
-by design, so the gate is statistical: per-pixel relative RMSE
-sqrt(mean((a-b)^2/(b^2+0.01))) <= TOL at equal sample counts, reported next to the noise
-floor between two independent oracle runs."""
+bit-exact with the reference renderer (tests/test_oracle_golden.py).
+
+The arithmetic of every path is pinned path by path in tests/test_gpu_paths.py.  What is left
+for this file is the one thing that cannot be compared path by path: the GPU's counter-based
+streams against the reference's own xorshift64* streams (seeded per thread per frame from the
+wall clock, engine.cpp:179).  That gate is statistical: per-pixel relative RMSE
+sqrt(mean((a-b)^2/(b^2+0.01))) at 1 024 samples per pixel (SURVEY 8(d) gate 3), for the whole
+image and per first-hit material region, next to the noise floor between two independent oracle
+runs; every number is written to gpurun_out/parity_rmse.json (committed as
+profiles/r2_parity_rmse.json)."""
+import json
+import os
+
 import numpy as np
 import pytest
 
@@ -11,11 +20,24 @@ from refdata import golden, rel_rmse
 
 pytestmark = pytest.mark.gpu
 
-SPP = 256
+SPP = 1024
 # stated tolerance: the two estimates are independent Monte-Carlo means, so their distance
-# is about sqrt(2) x the single-run noise; gate at 1.6 x the oracle-vs-oracle floor + 0.004.
+# is about sqrt(2) x the single-run noise; gate at 1.6 x the oracle-vs-oracle floor + 0.004,
+# and never above SURVEY 8(d)'s 0.02 + floor.
 FLOOR_FACTOR = 1.6
 SLACK = 0.004
+RMSE_REPORT = {}
+
+
+def _report(name, rec):
+    RMSE_REPORT[name] = rec
+    out = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "gpurun_out")
+    try:
+        os.makedirs(out, exist_ok=True)
+        with open(os.path.join(out, "parity_rmse.json"), "w") as f:
+            json.dump(RMSE_REPORT, f, indent=1, sort_keys=True)
+    except OSError:
+        pass
 
 
 def oracle_mean(g, w, h, frames, clock0):
@@ -27,7 +49,7 @@ def oracle_mean(g, w, h, frames, clock0):
                                   "demo_dof", "grid_tiny"])
 def test_converged_image_matches_oracle(ctx, name):
     g = golden(name)
-    w, h = 64, 40
+    w, h = 48, 32
     a = oracle_mean(g, w, h, SPP, 1700000000000)
     b = oracle_mean(g, w, h, SPP, 1800000000123)
     floor = rel_rmse(a, b)
@@ -39,7 +61,27 @@ def test_converged_image_matches_oracle(ctx, name):
     e1 = rel_rmse(film["mean"], a)
     e2 = rel_rmse(film["mean"], b)
     print("%s: gpu-vs-oracle %.4f / %.4f, oracle-vs-oracle floor %.4f" % (name, e1, e2, floor))
-    assert max(e1, e2) <= FLOOR_FACTOR * floor + SLACK
+    rec = {"spp": SPP, "width": w, "height": h, "gpu_vs_oracle": [e1, e2], "oracle_floor": floor,
+           "regions": {}}
+    assert max(e1, e2) <= min(FLOOR_FACTOR * floor + SLACK, floor + 0.02)
+    # per first-hit material region (a wrong constant in one material only moves its pixels):
+    # relative RMSE against the same gate, and the region's mean radiance within 3 standard
+    # errors of the oracle-vs-oracle difference (+ 0.5 %)
+    ids = binding.first_hit(g.scene, g.cam, w, h)["mat_id"]
+    both = 0.5 * (a.astype(np.float64) + b.astype(np.float64))
+    for mid in np.unique(ids):
+        m = ids == mid
+        if int(m.sum()) < 24:
+            continue
+        rf = rel_rmse(a[m], b[m])
+        re = max(rel_rmse(film["mean"][m], a[m]), rel_rmse(film["mean"][m], b[m]))
+        mean_gpu, mean_or = float(film["mean"][m].mean()), float(both[m].mean())
+        spread = abs(float(a[m].mean()) - float(b[m].mean()))
+        rec["regions"][str(int(mid))] = {"pixels": int(m.sum()), "gpu_vs_oracle": re, "oracle_floor": rf,
+                                         "mean_gpu": mean_gpu, "mean_oracle": mean_or}
+        assert re <= FLOOR_FACTOR * rf + 2 * SLACK, (name, int(mid), re, rf)
+        assert abs(mean_gpu - mean_or) <= 3.0 * spread + 0.005 * mean_or + 1e-3, (name, int(mid))
+    _report(name, rec)
     # mean brightness must agree much tighter than per-pixel noise (bias check)
     assert abs(film["mean"].mean() - a.mean()) <= 0.01 * a.mean() + 1e-3
 
