@@ -24,6 +24,8 @@ FS_TRACE_PER_THREAD = 32
 FS_TRACE_COOP = 64
 FS_TRACE_LBVH_LANE = 128
 FS_TRACE_MEGAKERNEL = 256
+FS_TRACE_SHARD_TILES = 512
+FS_TRACE_SHARD_SAMPLES = 1024
 
 # numpy dtypes of the flattened arrays -------------------------------------------------
 NODE_DT = np.dtype([("bmin", "<f4", 3), ("first", "<u4"), ("bmax", "<f4", 3), ("count", "<u4")])

@@ -56,6 +56,8 @@ int main(int argc, char** argv) {
   uint32 width = 800, height = 480, spp = 16;  // 800x480: source/main.cpp:53-54
   uint64 seed = 1;
   int device = 0;
+  std::vector<int> devices;  // --gpus N / --devices a,b,...: multi-device context
+  int shard_mode = 0;        // 0 automatic, 1 samples, 2 tiles
   bool fast = false, have_focus = false;
   PostProcess post;
   std::string post_out;
@@ -66,6 +68,19 @@ int main(int argc, char** argv) {
     if (!strcmp(a, "--spp")) spp = (uint32)atoi(next());
     else if (!strcmp(a, "--seed")) seed = strtoull(next(), nullptr, 10);
     else if (!strcmp(a, "--device")) device = atoi(next());
+    else if (!strcmp(a, "--gpus")) {  // the first N devices of the box
+      devices.clear();
+      for (int d = 0, n = atoi(next()); d < n; d++) devices.push_back(d);
+    } else if (!strcmp(a, "--devices")) {  // explicit list: 0,2,5
+      devices.clear();
+      for (const char* p = next(); *p;) {
+        devices.push_back((int)strtol(p, (char**)&p, 10));
+        if (*p == ',') p++;
+      }
+    } else if (!strcmp(a, "--shard")) {
+      const char* m = next();
+      shard_mode = !strcmp(m, "samples") ? 1 : !strcmp(m, "tiles") ? 2 : 0;
+    }
     else if (!strcmp(a, "--out")) out = next();
     else if (!strcmp(a, "--pfm")) pfm = next();
     else if (!strcmp(a, "--exr")) exr = next();
@@ -91,7 +106,7 @@ int main(int argc, char** argv) {
   }
   if (file.empty()) {  // source/main.cpp:78-81
     fprintf(stderr, "usage: fs2_render -f <scene file> [-w W] [-h H] [--spp N] [--seed S] "
-                    "[--device D] [--out image.ppm] [--pfm mean.pfm] [--exr mean.exr] [--focus x,y] [--fast] "
+                    "[--device D | --gpus N | --devices a,b,..] [--shard auto|samples|tiles] [--out image.ppm] [--pfm mean.pfm] [--exr mean.exr] [--focus x,y] [--fast] "
                     "[--resume film.ckpt] [--checkpoint film.ckpt] [--post-out image.ppm "
                     "[--denoise passes] [--bloom strength[,threshold[,radius]]] "
                     "[--flare strength[,ghosts]]]\n");
@@ -106,7 +121,12 @@ int main(int argc, char** argv) {
   if (scene.GetCameraCount()) cam = *scene.GetCamera(0);
   cam.fast_render_enabled = fast;
   DisplayFrame frame(width, height);
-  SetTraceDevice(device);
+  if (devices.size() > 1) {
+    SetTraceDevices(devices.data(), (int)devices.size());
+    SetTraceSharding(shard_mode);
+  } else {
+    SetTraceDevice(devices.empty() ? device : devices[0]);
+  }
   SetTraceSeed(seed);
   if (have_focus) {  // source/main.cpp:144-153
     cam.focal_depth = TraceRange(cam, &scene, &frame, fx, fy);
@@ -122,8 +142,9 @@ int main(int argc, char** argv) {
     return 1;
   }
   double sec = std::chrono::duration<double>(std::chrono::steady_clock::now() - t0).count();
-  printf("%ux%u, %u spp in %.3f s (%.2f Mpaths/s, scene upload included)\n", width, height, spp,
-         sec, (double)width * height * spp / sec / 1e6);
+  printf("%ux%u, %u spp on %d GPU%s in %.3f s (%.2f Mpaths/s, scene upload included)\n", width, height,
+         spp, GetTraceDeviceCount(), GetTraceDeviceCount() > 1 ? "s" : "", sec,
+         (double)width * height * spp / sec / 1e6);
   if (!checkpoint.empty() && !SaveFilmCheckpoint(&frame, checkpoint.c_str())) {
     fprintf(stderr, "cannot write %s: %s\n", checkpoint.c_str(), LastTraceError());
     return 1;

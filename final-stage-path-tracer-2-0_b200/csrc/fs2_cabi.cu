@@ -14,6 +14,7 @@
 #include <string.h>
 
 #include <string>
+#include <thread>
 #include <vector>
 
 #include <cub/device/device_scan.cuh>
@@ -69,6 +70,13 @@ struct fs_ctx {
   float last_trace_ms = 0.f, last_kernel_ms = 0.f;
   bool stats_build = false;
   uint32_t tune = 8;  // FS2_TUNE: bits 0-4 idle lanes that trigger a refill in k_wf_trace, bits 8.. pool size (1024 paths)
+  // interleaved tile sharding of this context (fs_set_tile_shard); tile_n <= 1: every tile
+  uint32_t tile_n = 1, tile_r = 0;
+  // multi-device lead (fs_create_multi): the contexts on the other devices, in device order
+  std::vector<fs_ctx*> peers;
+  std::vector<int> peer_direct;  // 1: the lead reads that peer's film through a peer mapping
+  DeviceBuf stage;               // staged copies of peer films when there is no peer mapping
+  fs_ctx* lead = nullptr;        // set on peers
 };
 
 namespace {
@@ -304,7 +312,10 @@ int collect_timing(fs_ctx* ctx) {
 //    and stops enqueueing once a wave reported zero live paths; the waves already in the
 //    queue then exit at once.
 int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
-  const uint32_t tiles_x = (uint32_t)(film.width + 15) / 16, tiles_y = (uint32_t)(film.height + 7) / 8;
+  uint32_t tiles_x = (uint32_t)(film.width + 15) / 16;
+  const uint32_t tiles_y = (uint32_t)(film.height + 7) / 8;
+  const uint32_t tile_n = ctx->tile_n > 1 ? ctx->tile_n : 1u;
+  if (tile_n > 1) tiles_x = (tiles_x + tile_n - 1) / tile_n;  // this shard's tiles per row
   const uint32_t pix_cap = tiles_x * tiles_y * 128u;
   const unsigned long long total = (unsigned long long)pix_cap * tp.n_samples;
   unsigned long long pool = FS2_WF_MAX_PATHS;
@@ -349,6 +360,8 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
     B[p].pix_cap = pix_cap;
     B[p].tiles_x = tiles_x;
     B[p].total = total;
+    B[p].tile_n = tile_n;
+    B[p].tile_r = ctx->tile_r;
     streams[p] = p == 0 ? ctx->stream : ctx->wf_stream;
     *(volatile uint32_t*)(ctx->wf_host_live + p) = 1u;
   }
@@ -421,11 +434,9 @@ int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const Tr
   return rc;
 }
 
-// Builds the leaf BVHs of `s` (host threads) and uploads them; the host vectors must outlive the
-// asynchronous copies, hence the synchronisation.
-int upload_lbvh(fs_ctx* ctx, const fs_scene_desc* s, float m_floor_min) {
-  LbvhHost lb;
-  build_lbvh(s, &lb, 9, 0, m_floor_min);
+// Uploads prebuilt leaf BVHs; the host vectors must outlive the asynchronous copies, hence the
+// synchronisation.
+int upload_lbvh(fs_ctx* ctx, const LbvhHost& lb) {
   int rc;
   if ((rc = dev_upload(ctx, &ctx->lb_nodes, lb.nodes.data(), lb.nodes.size() * sizeof(LbNode)))) return rc;
   if ((rc = dev_upload(ctx, &ctx->lb_leaf, lb.leaf.data(), lb.leaf.size() * sizeof(LbLeaf)))) return rc;
@@ -441,6 +452,54 @@ int upload_lbvh(fs_ctx* ctx, const fs_scene_desc* s, float m_floor_min) {
   d.lb_order = (const uint32_t*)ctx->lb_order.p;
   d.lb_origin_limit = lb.origin_limit();
   ctx->lb_m_floor = lb.m_floor;
+  return FS_OK;
+}
+
+// The lead context followed by its peers (a plain context: itself only).
+std::vector<fs_ctx*> all_contexts(fs_ctx* ctx) {
+  std::vector<fs_ctx*> all{ctx};
+  all.insert(all.end(), ctx->peers.begin(), ctx->peers.end());
+  return all;
+}
+
+// One device's copy of the (validated) scene.
+int scene_upload_one(fs_ctx* ctx, const fs_scene_desc* s, const std::vector<float>& lut4,
+                     const LbvhHost& lb) {
+  int rc;
+  if ((rc = set_device(ctx))) return rc;
+  ctx->have_scene = false;
+  if ((rc = dev_upload(ctx, &ctx->nodes, s->nodes, (size_t)s->n_nodes * sizeof(fs_node)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->scene_refs, s->scene_refs, (size_t)s->n_scene_refs * 4))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->tri_plane, s->tri_plane, (size_t)s->n_tris * 16))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->tri_aux, s->tri_aux, (size_t)s->n_tris * sizeof(fs_tri_aux)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->faces, s->faces, (size_t)s->n_faces * sizeof(fs_face_attr)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->objects, s->objects, (size_t)s->n_objects * sizeof(fs_object)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->materials, s->materials, (size_t)s->n_materials * sizeof(fs_material)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->textures, s->textures, (size_t)s->n_textures * sizeof(fs_texture)))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->texels, s->texels, (size_t)s->n_texels * 4))) return rc;
+  if ((rc = dev_upload(ctx, &ctx->lut, lut4.data(), lut4.size() * 4))) return rc;
+  if ((rc = upload_lbvh(ctx, lb))) return rc;  // synchronises the stream
+  DScene& d = ctx->ds;
+  d.nodes = (const float4*)ctx->nodes.p;
+  d.scene_refs = (const uint32_t*)ctx->scene_refs.p;
+  d.tri_plane = (const float4*)ctx->tri_plane.p;
+  d.tri_aux = (const float4*)ctx->tri_aux.p;
+  d.faces = (const float4*)ctx->faces.p;
+  d.objects = (const float4*)ctx->objects.p;
+  d.materials = (const float4*)ctx->materials.p;
+  d.textures = (const fs_texture*)ctx->textures.p;
+  d.texels = (const float*)ctx->texels.p;
+  d.lut = (const float4*)ctx->lut.p;
+  d.n_objects = s->n_objects;
+  d.n_lut = s->n_lut;
+  d.sky_material = s->sky_material;
+  d.scene_root = s->scene_root;
+  ctx->n_nodes = s->n_nodes;
+  ctx->n_tris = s->n_tris;
+  ctx->n_faces = s->n_faces;
+  ctx->n_materials = s->n_materials;
+  ctx->n_objects = s->n_objects;
+  ctx->have_scene = true;
   return FS_OK;
 }
 
@@ -472,7 +531,9 @@ int ensure_lbvh_for_camera(fs_ctx* ctx, const fs_camera* cam) {
   d.tri_aux = aux.data();
   d.objects = objects.data();
   if (ctx->wf_stream) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->wf_stream));
-  return upload_lbvh(ctx, &d, m / 2.0f);  // limit = 3 * m_floor >= 1.5 * |camera|
+  LbvhHost lb;
+  build_lbvh(&d, &lb, 9, 0, m / 2.0f);  // limit = 3 * m_floor >= 1.5 * |camera|
+  return upload_lbvh(ctx, lb);
 }
 
 #include "fs2_build_host.inc"
@@ -540,15 +601,72 @@ int fs_create(fs_ctx** out, int device, int flags) {
   return FS_OK;
 }
 
+int fs_create_multi(fs_ctx** out, const int* device_ids, int n_devices, int flags) {
+  if (!out) return fail(nullptr, FS_E_INVALID, "fs_create_multi: null out pointer");
+  *out = nullptr;
+  if (!device_ids || n_devices < 1 || n_devices > FS2_MAX_DEVICES)
+    return fail(nullptr, FS_E_INVALID, "fs_create_multi: 1..%d devices", FS2_MAX_DEVICES);
+  for (int i = 0; i < n_devices; i++)
+    for (int j = 0; j < i; j++)
+      if (device_ids[i] == device_ids[j])
+        return fail(nullptr, FS_E_INVALID, "fs_create_multi: device %d listed twice", device_ids[i]);
+  fs_ctx* lead = nullptr;
+  int rc = fs_create(&lead, device_ids[0], flags);
+  if (rc) return rc;
+  for (int i = 1; i < n_devices; i++) {
+    fs_ctx* peer = nullptr;
+    if ((rc = fs_create(&peer, device_ids[i], flags))) {
+      fs_destroy(lead);
+      return rc;
+    }
+    peer->lead = lead;
+    lead->peers.push_back(peer);
+    // the combine kernel on the lead reads the peer's film over NVLink when a peer mapping
+    // exists; otherwise the film is staged through cudaMemcpyPeerAsync
+    int can = 0;
+    cudaSetDevice(lead->device);
+    if (cudaDeviceCanAccessPeer(&can, lead->device, peer->device) == cudaSuccess && can) {
+      cudaError_t e = cudaDeviceEnablePeerAccess(peer->device, 0);
+      if (e == cudaErrorPeerAccessAlreadyEnabled) {
+        cudaGetLastError();
+        e = cudaSuccess;
+      }
+      can = e == cudaSuccess;
+      if (!can) cudaGetLastError();
+    }
+    lead->peer_direct.push_back(can ? 1 : 0);
+  }
+  *out = lead;
+  return FS_OK;
+}
+
+int fs_device_count(const fs_ctx* ctx) { return ctx ? 1 + (int)ctx->peers.size() : 0; }
+
+int fs_set_tile_shard(fs_ctx* ctx, int rank, int world) {
+  if (!ctx || world < 1 || rank < 0 || rank >= world || world > 65535)
+    return fail(ctx, FS_E_INVALID, "fs_set_tile_shard: bad rank %d of %d", rank, world);
+  if (!ctx->peers.empty())
+    return fail(ctx, FS_E_INVALID, "fs_set_tile_shard: a multi-device context shards by itself");
+  ctx->tile_n = (uint32_t)world;
+  ctx->tile_r = (uint32_t)rank;
+  return FS_OK;
+}
+
 int fs_destroy(fs_ctx* ctx) {
   if (!ctx) return FS_OK;
+  for (fs_ctx* p : ctx->peers) {
+    p->lead = nullptr;
+    fs_destroy(p);
+  }
+  ctx->peers.clear();
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
   DeviceBuf* all[] = {&ctx->nodes, &ctx->scene_refs, &ctx->tri_plane, &ctx->tri_aux, &ctx->faces,
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
                       &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,
-                      &ctx->scratch, &ctx->auxpack, &ctx->post, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters};
+                      &ctx->scratch, &ctx->auxpack, &ctx->post, &ctx->wf_planes, &ctx->wf_hit, &ctx->wf_counters,
+                      &ctx->stage};
   for (DeviceBuf* b : all) dev_free(b);
   if (ctx->d_stats) cudaFree(ctx->d_stats);
   if (ctx->wf_host_live) {
@@ -571,8 +689,6 @@ int fs_scene_upload(fs_ctx* ctx, const fs_scene_desc* s) {
   if (!ctx || !s) return fail(ctx, FS_E_INVALID, "fs_scene_upload: null argument");
   int rc = validate_scene(ctx, s);
   if (rc) return rc;
-  if ((rc = set_device(ctx))) return rc;
-  ctx->have_scene = false;
   // LUT repacked to 16 bytes per entry so one ld.global.v4 fetches a normal
   std::vector<float> lut4((size_t)s->n_lut * 4);
   for (uint32_t i = 0; i < s->n_lut; i++) {
@@ -581,45 +697,30 @@ int fs_scene_upload(fs_ctx* ctx, const fs_scene_desc* s) {
     lut4[4 * (size_t)i + 2] = s->lut[3 * (size_t)i + 2];
     lut4[4 * (size_t)i + 3] = 0.f;
   }
-  if ((rc = dev_upload(ctx, &ctx->nodes, s->nodes, (size_t)s->n_nodes * sizeof(fs_node)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->scene_refs, s->scene_refs, (size_t)s->n_scene_refs * 4))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->tri_plane, s->tri_plane, (size_t)s->n_tris * 16))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->tri_aux, s->tri_aux, (size_t)s->n_tris * sizeof(fs_tri_aux)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->faces, s->faces, (size_t)s->n_faces * sizeof(fs_face_attr)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->objects, s->objects, (size_t)s->n_objects * sizeof(fs_object)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->materials, s->materials, (size_t)s->n_materials * sizeof(fs_material)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->textures, s->textures, (size_t)s->n_textures * sizeof(fs_texture)))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->texels, s->texels, (size_t)s->n_texels * 4))) return rc;
-  if ((rc = dev_upload(ctx, &ctx->lut, lut4.data(), lut4.size() * 4))) return rc;
-  // leaf BVH over every mesh-tree leaf (fs2_lbvh_build.h)
-  if ((rc = upload_lbvh(ctx, s, 0.0f))) return rc;
-  DScene& d = ctx->ds;
-  d.nodes = (const float4*)ctx->nodes.p;
-  d.scene_refs = (const uint32_t*)ctx->scene_refs.p;
-  d.tri_plane = (const float4*)ctx->tri_plane.p;
-  d.tri_aux = (const float4*)ctx->tri_aux.p;
-  d.faces = (const float4*)ctx->faces.p;
-  d.objects = (const float4*)ctx->objects.p;
-  d.materials = (const float4*)ctx->materials.p;
-  d.textures = (const fs_texture*)ctx->textures.p;
-  d.texels = (const float*)ctx->texels.p;
-  d.lut = (const float4*)ctx->lut.p;
-  d.n_objects = s->n_objects;
-  d.n_lut = s->n_lut;
-  d.sky_material = s->sky_material;
-  d.scene_root = s->scene_root;
-  ctx->n_nodes = s->n_nodes;
-  ctx->n_tris = s->n_tris;
-  ctx->n_faces = s->n_faces;
-  ctx->n_materials = s->n_materials;
-  ctx->n_objects = s->n_objects;
-  ctx->have_scene = true;
+  // leaf BVH over every mesh-tree leaf (fs2_lbvh_build.h): built once, uploaded to every device
+  LbvhHost lb;
+  build_lbvh(s, &lb, 9, 0, 0.0f);
+  if (ctx->peers.empty()) return scene_upload_one(ctx, s, lut4, lb);
+  // multi-device lead: the scene is replicated, one host thread per device
+  std::vector<fs_ctx*> all = all_contexts(ctx);
+  std::vector<int> rcs(all.size(), FS_OK);
+  std::vector<std::thread> workers;
+  for (size_t i = 1; i < all.size(); i++)
+    workers.emplace_back([&, i]() { rcs[i] = scene_upload_one(all[i], s, lut4, lb); });
+  rcs[0] = scene_upload_one(ctx, s, lut4, lb);
+  for (std::thread& t : workers) t.join();
+  for (size_t i = 0; i < all.size(); i++)
+    if (rcs[i]) return i ? fail(ctx, rcs[i], "device %d: %s", all[i]->device, all[i]->error) : rcs[i];
   return FS_OK;
 }
 
 int fs_film_resize(fs_ctx* ctx, int width, int height) {
   if (!ctx || width <= 0 || height <= 0 || (int64_t)width * height > (1ll << 30))
     return fail(ctx, FS_E_INVALID, "fs_film_resize: bad size %dx%d", width, height);
+  for (fs_ctx* p : ctx->peers) {
+    int prc = fs_film_resize(p, width, height);
+    if (prc) return fail(ctx, prc, "device %d: %s", p->device, p->error);
+  }
   int rc = set_device(ctx);
   if (rc) return rc;
   size_t n = (size_t)width * height;
@@ -637,6 +738,10 @@ int fs_film_resize(fs_ctx* ctx, int width, int height) {
 int fs_film_reset(fs_ctx* ctx) {
   if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
   if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_reset before fs_film_resize");
+  for (fs_ctx* p : ctx->peers) {
+    int prc = fs_film_reset(p);
+    if (prc) return fail(ctx, prc, "device %d: %s", p->device, p->error);
+  }
   int rc = set_device(ctx);
   if (rc) return rc;
   size_t n = (size_t)ctx->width * ctx->height;
@@ -728,8 +833,9 @@ int fs_film_resolve(fs_ctx* ctx) {
   return FS_OK;
 }
 
-int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t n_samples,
-             uint32_t sample_stride, uint64_t seed, int flags) {
+// First half of fs_trace on one device: the path-tracing kernels of this context's shard.
+static int trace_begin(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t n_samples,
+                       uint32_t sample_stride, uint64_t seed, int flags) {
   if (!ctx || !cam) return fail(ctx, FS_E_INVALID, "fs_trace: null argument");
   if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_trace before fs_scene_upload");
   if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_trace before fs_film_resize");
@@ -774,6 +880,11 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
     CUDA_TRY(ctx, cudaGetLastError());
   }
   CUDA_TRY(ctx, cudaEventRecord(ctx->evk1, ctx->stream));
+  return FS_OK;
+}
+
+// Second half: resolve (mean, gamma, RGB8), timing events, synchronisation.
+static int trace_finish(fs_ctx* ctx, int flags) {
   if (!(flags & FS_TRACE_NO_RESOLVE)) {
     int n = ctx->width * ctx->height;
     k_resolve<<<(n + 255) / 256, 256, 0, ctx->stream>>>(
@@ -787,6 +898,115 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t 
   if (flags & FS_TRACE_ASYNC) return FS_OK;
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return collect_timing(ctx);
+}
+
+// Multi-device lead: shard, trace on every device (one host thread each, like the reference fans
+// TraceScene out over its worker threads, engine.cpp:261-274), combine the films on the lead.
+//  * sample sharding: device r takes the requested samples j with j == (n - 1 - r) mod N, so the
+//    lead owns the last sample (whose depth-0 hit fills the aux planes, frame.cpp:78-85);
+//  * tile sharding: every device traces all samples of the 16x8-pixel tiles (tx, ty) with
+//    (tx + ty) mod N == r (diagonal interleave).  Chosen when there are fewer samples than
+//    devices, or on request; the combine then moves one film in total instead of N - 1.
+static int trace_multi(fs_ctx* lead, const fs_camera* cam, uint32_t first_sample, uint32_t n_samples,
+                       uint32_t sample_stride, uint64_t seed, int flags) {
+  if (!lead->have_scene) return fail(lead, FS_E_NOSCENE, "fs_trace before fs_scene_upload");
+  if (!lead->width) return fail(lead, FS_E_NOFILM, "fs_trace before fs_film_resize");
+  std::vector<fs_ctx*> all = all_contexts(lead);
+  const uint32_t N = (uint32_t)all.size();
+  const int mega = FS_TRACE_PER_THREAD | FS_TRACE_COOP | FS_TRACE_LBVH_LANE | FS_TRACE_MEGAKERNEL;
+  bool tiles = (flags & FS_TRACE_SHARD_TILES) || (!(flags & FS_TRACE_SHARD_SAMPLES) && n_samples < N);
+  if (tiles && (flags & mega)) {
+    if (flags & FS_TRACE_SHARD_TILES)
+      return fail(lead, FS_E_INVALID, "fs_trace: tile sharding needs the default (wavefront) pipeline");
+    tiles = false;
+  }
+  if (sample_stride == 0) sample_stride = 1;
+  const size_t n_px = (size_t)lead->width * lead->height;
+  const int inner = (flags | FS_TRACE_NO_RESOLVE) & ~(FS_TRACE_SHARD_TILES | FS_TRACE_SHARD_SAMPLES);
+  std::vector<int> rcs(N, FS_OK);
+  auto run = [&](uint32_t r) {
+    fs_ctx* c = all[r];
+    uint32_t first = first_sample, count = n_samples, stride = sample_stride;
+    if (tiles) {
+      c->tile_n = N;
+      c->tile_r = r;
+    } else {
+      c->tile_n = 1;
+      c->tile_r = 0;
+      // samples jr, jr + N, ... below n_samples; devices beyond the sample count get none
+      const uint32_t jr = (uint32_t)(((uint64_t)n_samples + N - 1 - r) % N);  // (n - 1 - r) mod N
+      count = n_samples > jr ? (n_samples - jr + N - 1) / N : 0;
+      first = first_sample + jr * sample_stride;
+      stride = sample_stride * N;
+    }
+    int rc = set_device(c);
+    if (!rc && r) {
+      // a peer's film holds this call's contribution only
+      if (cudaMemsetAsync(c->sum.p, 0, n_px * 16, c->stream) != cudaSuccess)
+        rc = fail(c, FS_E_CUDA, "cudaMemsetAsync(peer film)");
+    }
+    if (!rc) rc = trace_begin(c, cam, first, count, stride, seed, r ? (inner & ~FS_TRACE_ASYNC) : inner);
+    if (!rc && r && cudaStreamSynchronize(c->stream) != cudaSuccess)
+      rc = fail(c, FS_E_CUDA, "cudaStreamSynchronize(peer): %s", cudaGetErrorString(cudaGetLastError()));
+    c->tile_n = 1;
+    c->tile_r = 0;
+    rcs[r] = rc;
+  };
+  std::vector<std::thread> workers;
+  for (uint32_t r = 1; r < N; r++) workers.emplace_back(run, r);
+  run(0);
+  for (std::thread& t : workers) t.join();
+  int rc = set_device(lead);
+  for (uint32_t r = 0; r < N && !rc; r++)
+    if (rcs[r]) rc = r ? fail(lead, rcs[r], "device %d: %s", all[r]->device, all[r]->error) : rcs[r];
+  if (rc) {
+    cudaStreamSynchronize(lead->stream);
+    cudaGetLastError();
+    return rc;
+  }
+  // combine on the lead, in device order
+  PeerFilms pf;
+  memset(&pf, 0, sizeof pf);
+  pf.n_peers = (int)N - 1;
+  pf.tile_n = tiles ? (int)N : 0;
+  const size_t per_peer = n_px * (tiles ? 36 : 16);
+  bool need_stage = false;
+  for (uint32_t r = 1; r < N; r++) need_stage |= !lead->peer_direct[r - 1];
+  if (need_stage && (rc = dev_alloc(lead, &lead->stage, per_peer * (N - 1)))) return rc;
+  for (uint32_t r = 1; r < N; r++) {
+    fs_ctx* c = all[r];
+    if (lead->peer_direct[r - 1]) {
+      pf.sum[r - 1] = (const float4*)c->sum.p;
+      pf.aux[r - 1] = (const float4*)c->aux.p;
+      pf.mat_id[r - 1] = (const uint32_t*)c->mat_id.p;
+    } else {
+      char* base = (char*)lead->stage.p + per_peer * (r - 1);
+      CUDA_TRY(lead, cudaMemcpyPeerAsync(base, lead->device, c->sum.p, c->device, n_px * 16, lead->stream));
+      pf.sum[r - 1] = (const float4*)base;
+      if (tiles) {
+        CUDA_TRY(lead, cudaMemcpyPeerAsync(base + n_px * 16, lead->device, c->aux.p, c->device, n_px * 16, lead->stream));
+        CUDA_TRY(lead, cudaMemcpyPeerAsync(base + n_px * 32, lead->device, c->mat_id.p, c->device, n_px * 4, lead->stream));
+        pf.aux[r - 1] = (const float4*)(base + n_px * 16);
+        pf.mat_id[r - 1] = (const uint32_t*)(base + n_px * 32);
+      }
+    }
+  }
+  k_film_combine<<<(unsigned)((n_px + 255) / 256), 256, 0, lead->stream>>>(
+      (float4*)lead->sum.p, (float4*)lead->aux.p, (uint32_t*)lead->mat_id.p, pf, lead->width, (int)n_px);
+  lead->launches++;
+  CUDA_TRY(lead, cudaGetLastError());
+  // the peers' films may be cleared by the next call only after the combine has read them
+  if ((rc = trace_finish(lead, flags & ~FS_TRACE_ASYNC))) return rc;
+  return FS_OK;
+}
+
+int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample, uint32_t n_samples,
+             uint32_t sample_stride, uint64_t seed, int flags) {
+  if (!ctx || !cam) return fail(ctx, FS_E_INVALID, "fs_trace: null argument");
+  if (!ctx->peers.empty()) return trace_multi(ctx, cam, first_sample, n_samples, sample_stride, seed, flags);
+  int rc = trace_begin(ctx, cam, first_sample, n_samples, sample_stride, seed, flags);
+  if (rc) return rc;
+  return trace_finish(ctx, flags);
 }
 
 int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8, float* normal,
@@ -929,6 +1149,15 @@ int fs_film_device(fs_ctx* ctx, void** sum_rgba, size_t* n_floats) {
   return FS_OK;
 }
 
+int fs_film_device_aux(fs_ctx* ctx, void** aux_xyzd, void** mat_id_u32, size_t* n_pixels) {
+  if (!ctx || !aux_xyzd || !mat_id_u32 || !n_pixels) return fail(ctx, FS_E_INVALID, "null argument");
+  if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_device_aux before fs_film_resize");
+  *aux_xyzd = ctx->aux.p;
+  *mat_id_u32 = ctx->mat_id.p;
+  *n_pixels = (size_t)ctx->width * ctx->height;
+  return FS_OK;
+}
+
 int fs_film_save(fs_ctx* ctx, float* sum_rgba) {
   if (!ctx || !sum_rgba) return fail(ctx, FS_E_INVALID, "null argument");
   if (!ctx->width) return fail(ctx, FS_E_NOFILM, "fs_film_save before fs_film_resize");
@@ -946,6 +1175,12 @@ int fs_film_load(fs_ctx* ctx, const float* sum_rgba) {
   int rc = set_device(ctx);
   if (rc) return rc;
   size_t n = (size_t)ctx->width * ctx->height;
+  // the sample count rides in the float w channel: exact below 2^24 samples per pixel only
+  for (size_t i = 0; i < n; i++) {
+    float c = sum_rgba[4 * i + 3];
+    if (!(c >= 0.0f && c < 16777216.0f) || c != floorf(c))
+      return fail(ctx, FS_E_INVALID, "fs_film_load: pixel %zu has sample count %g (must be an integer below 2^24)", i, (double)c);
+  }
   CUDA_TRY(ctx, cudaMemcpyAsync(ctx->sum.p, sum_rgba, n * 16, cudaMemcpyHostToDevice, ctx->stream));
   return fs_film_resolve(ctx);
 }
@@ -971,11 +1206,26 @@ int fs_get_stats(fs_ctx* ctx, fs_stats* out) {
   out->launches = ctx->launches;
   out->last_trace_ms = ctx->last_trace_ms;
   out->last_kernel_ms = ctx->last_kernel_ms;
-  return FS_OK;
+  for (fs_ctx* p : ctx->peers) {  // multi-device lead: work counters of the whole job
+    fs_stats ps;
+    if ((rc = fs_get_stats(p, &ps))) return fail(ctx, rc, "device %d: %s", p->device, p->error);
+    out->n_paths += ps.n_paths;
+    out->n_segments += ps.n_segments;
+    out->n_node += ps.n_node;
+    out->n_tri += ps.n_tri;
+    out->n_bary += ps.n_bary;
+    out->n_prim += ps.n_prim;
+    out->n_shade += ps.n_shade;
+    out->n_lbnode += ps.n_lbnode;
+    out->n_tritest += ps.n_tritest;
+    out->launches += ps.launches;
+  }
+  return set_device(ctx);
 }
 
 int fs_reset_stats(fs_ctx* ctx) {
   if (!ctx) return fail(ctx, FS_E_INVALID, "null context");
+  for (fs_ctx* p : ctx->peers) fs_reset_stats(p);
   int rc = set_device(ctx);
   if (rc) return rc;
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->d_stats, 0, ST_COUNT * sizeof(unsigned long long), ctx->stream));

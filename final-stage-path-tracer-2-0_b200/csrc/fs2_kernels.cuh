@@ -421,6 +421,47 @@ k_unpack_aux(const float4* __restrict__ aux, const uint32_t* __restrict__ ids, i
   id64[i] = ids[i];
 }
 
+// Multi-device film combine (fs_create_multi): runs on the lead device and reads the other
+// devices' films through NVLink peer pointers (or staged copies of them), in device order, so
+// the N-GPU film is a deterministic function of the per-device films.
+//   sample sharding: every device holds partial sums of every pixel: sum += sum of peers; the
+//                    aux planes stay the lead's (it owns the last sample, frame.cpp:78-85)
+//   tile sharding:   pixel (x, y) lives on device (tx + ty) mod n only: add that one film's
+//                    value and take its aux planes (traffic: one film in total, not n - 1)
+#define FS2_MAX_DEVICES 16
+struct PeerFilms {
+  const float4* sum[FS2_MAX_DEVICES - 1];
+  const float4* aux[FS2_MAX_DEVICES - 1];
+  const uint32_t* mat_id[FS2_MAX_DEVICES - 1];
+  int n_peers;
+  int tile_n;  // 0: sample sharding
+};
+
+__global__ void __launch_bounds__(256)
+k_film_combine(float4* __restrict__ sum, float4* __restrict__ aux, uint32_t* __restrict__ mat_id,
+               PeerFilms P, int width, int n) {
+  int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  if (P.tile_n > 1) {
+    int x = i % width, y = i / width;
+    int owner = ((x >> 4) + (y >> 3)) % P.tile_n;
+    if (owner == 0) return;
+    float4 a = sum[i], b = __ldcs(P.sum[owner - 1] + i);
+    sum[i] = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+    if (b.w > 0.0f) {
+      aux[i] = __ldcs(P.aux[owner - 1] + i);
+      mat_id[i] = __ldcs(P.mat_id[owner - 1] + i);
+    }
+    return;
+  }
+  float4 a = sum[i];
+  for (int p = 0; p < P.n_peers; p++) {
+    float4 b = __ldcs(P.sum[p] + i);
+    a = make_float4(a.x + b.x, a.y + b.y, a.z + b.z, a.w + b.w);
+  }
+  sum[i] = a;
+}
+
 // reference source/frame.cpp:56-69: mean and display RGB8 = 255*pow(sat(mean), 1/2.2) + 0.5
 __global__ void __launch_bounds__(256)
 k_resolve(const float4* __restrict__ sum, int n, float* __restrict__ mean_rgb,

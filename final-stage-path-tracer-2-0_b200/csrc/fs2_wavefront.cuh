@@ -57,9 +57,12 @@ struct WfBuffers {
   unsigned long long* next_path;  // next path id; shared by the pipelines of one fs_trace
   uint32_t* host_live;  // pinned host word: live paths at the start of the newest wave
   uint32_t cap;         // paths in flight
-  uint32_t pix_cap;     // pixel slots = padded 16x8 tiles x 128
-  uint32_t tiles_x;
+  uint32_t pix_cap;     // pixel slots = padded 16x8 tiles x 128 (this shard's tiles only)
+  uint32_t tiles_x;     // tiles per row of this shard's slot space
   unsigned long long total;  // path ids: pix_cap x n_samples (ids of padding pixels are skipped)
+  // interleaved tile sharding (fs_set_tile_shard): this context renders the 16x8-pixel tiles
+  // (tx, ty) with (tx + ty) mod tile_n == tile_r; slot space row ty holds tiles_x of them
+  uint32_t tile_n, tile_r;
 };
 
 // plane layout
@@ -71,8 +74,11 @@ struct WfBuffers {
 __device__ __forceinline__ void wf_slot_pixel(const WfBuffers& B, uint32_t slot, int& px, int& py) {
   uint32_t block = slot >> 7, t = slot & 127u;
   uint32_t lane = t & 31u, warp = t >> 5;
-  px = (int)((block % B.tiles_x) * 16u + (warp & 1u) * 8u + (lane & 7u));
-  py = (int)((block / B.tiles_x) * 8u + (warp >> 1) * 4u + (lane >> 3));
+  uint32_t tx = block % B.tiles_x, ty = block / B.tiles_x;
+  if (B.tile_n > 1u)  // k-th tile of row ty owned by this shard (diagonal interleave)
+    tx = tx * B.tile_n + (B.tile_r + B.tile_n - ty % B.tile_n) % B.tile_n;
+  px = (int)(tx * 16u + (warp & 1u) * 8u + (lane & 7u));
+  py = (int)(ty * 8u + (warp >> 1) * 4u + (lane >> 3));
 }
 
 // physical index of the i-th path of a wave with n_sec continuing paths

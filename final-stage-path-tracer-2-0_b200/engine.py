@@ -21,6 +21,11 @@ _SYMBOLS = {
     "fs_mesh_tree_free": (None, [C.POINTER(abi.fs_mesh_tree)]),
     "fs_last_error": (C.c_char_p, [C.c_void_p]),
     "fs_create": (C.c_int, [C.POINTER(C.c_void_p), C.c_int, C.c_int]),
+    "fs_create_multi": (C.c_int, [C.POINTER(C.c_void_p), C.POINTER(C.c_int), C.c_int, C.c_int]),
+    "fs_device_count": (C.c_int, [C.c_void_p]),
+    "fs_set_tile_shard": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
+    "fs_film_device_aux": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.POINTER(C.c_void_p),
+                                     C.POINTER(C.c_size_t)]),
     "fs_destroy": (C.c_int, [C.c_void_p]),
     "fs_scene_upload": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_scene_desc)]),
     "fs_film_resize": (C.c_int, [C.c_void_p, C.c_int, C.c_int]),
@@ -93,15 +98,23 @@ def _ptr(a):
 
 
 class Context:
-    """One fs_ctx: a scene resident on one GPU plus its film."""
+    """One fs_ctx: a scene resident on one GPU plus its film — or, with `devices=[...]`, one
+    multi-device context (fs_create_multi): the scene replicated on every listed GPU, fs_trace
+    sharded across them, the film combined on devices[0]."""
 
-    def __init__(self, device=0, stats=False):
+    def __init__(self, device=0, stats=False, devices=None):
         self.lib = load_library()
         self.handle = C.c_void_p()
-        rc = self.lib.fs_create(C.byref(self.handle), device, 1 if stats else 0)
+        if devices is not None:
+            ids = (C.c_int * len(devices))(*devices)
+            rc = self.lib.fs_create_multi(C.byref(self.handle), ids, len(devices), 1 if stats else 0)
+            device = devices[0] if len(devices) else 0
+        else:
+            rc = self.lib.fs_create(C.byref(self.handle), device, 1 if stats else 0)
         if rc != 0:
             raise Fs2Error(rc, (self.lib.fs_last_error(None) or b"").decode())
         self.device = device
+        self.devices = list(devices) if devices is not None else [device]
         self.width = self.height = 0
 
     def _check(self, rc):
@@ -210,6 +223,17 @@ class Context:
         n = C.c_size_t()
         self._check(self.lib.fs_film_device(self.handle, C.byref(p), C.byref(n)))
         return p.value, n.value
+
+    def film_device_aux(self):
+        """(aux pointer, material-id pointer, pixel count): float4 normal+depth and u32 id planes."""
+        a, m = C.c_void_p(), C.c_void_p()
+        n = C.c_size_t()
+        self._check(self.lib.fs_film_device_aux(self.handle, C.byref(a), C.byref(m), C.byref(n)))
+        return a.value, m.value, n.value
+
+    def set_tile_shard(self, rank, world):
+        """Multi-process tile sharding: render only the tiles (tx + ty) % world == rank."""
+        self._check(self.lib.fs_set_tile_shard(self.handle, rank, world))
 
     def stream(self):
         p = C.c_void_p()

@@ -41,12 +41,25 @@ def load_host_library():
     lib.fs2h_trace_range.argtypes = [C.c_void_p, C.POINTER(abi.fs_camera), C.c_void_p,
                                      C.c_float, C.c_float]
     lib.fs2h_set_device.argtypes = [C.c_int]
+    lib.fs2h_set_devices.argtypes = [C.POINTER(C.c_int), C.c_int]
+    lib.fs2h_set_sharding.argtypes = [C.c_int]
+    lib.fs2h_device_count.restype = C.c_int
+    lib.fs2h_scene_add_fog_cuboid.argtypes = [C.c_void_p, C.POINTER(C.c_float)]
     lib.fs2h_set_seed.argtypes = [C.c_uint64]
     lib.fs2h_set_gpu_build.argtypes = [C.c_int]
     lib.fs2h_gpu_build_ms.restype = C.c_float
     lib.fs2h_last_error.restype = C.c_char_p
     _lib = lib
     return lib
+
+
+def set_trace_devices(devices, sharding=0):
+    """base::SetTraceDevices: the GPUs behind TraceScene / TraceSamples; sharding 0 automatic,
+    1 sample indices, 2 interleaved tiles."""
+    lib = load_host_library()
+    ids = (C.c_int * len(devices))(*devices)
+    lib.fs2h_set_devices(ids, len(devices))
+    lib.fs2h_set_sharding(sharding)
 
 
 def _np_view(ptr, count, dtype):
@@ -92,6 +105,13 @@ class HostScene:
         cam = abi.fs_camera()
         self.lib.fs2h_scene_camera(self.handle, index, C.byref(cam))
         return cam
+
+    def add_fog_cuboid(self, position, size, rotation, colour, density):
+        """FogMaterial cuboid through the mirrored C++ API (not expressible in a .scene file)."""
+        v = (C.c_float * 14)(*position, *size, *rotation, *colour, density)
+        if self.lib.fs2h_scene_add_fog_cuboid(self.handle, v) != 0:
+            raise RuntimeError("AddCuboidObject failed")
+        self._desc = None
 
     def save_blob(self, path):
         if self.lib.fs2h_scene_save_blob(self.handle, os.fsencode(path)) != 0:

@@ -5,6 +5,8 @@
 #include <stdio.h>
 #include <string.h>
 
+#include <algorithm>
+#include <memory>
 #include <vector>
 
 #include "fs2_impl.h"
@@ -14,6 +16,9 @@ namespace {
 
 struct TraceState {
   int device = 0;
+  std::vector<int> devices;  // SetTraceDevices: more than one -> multi-device context
+  bool devices_changed = false;
+  int shard_flags = 0;       // FS_TRACE_SHARD_TILES / FS_TRACE_SHARD_SAMPLES / 0 = automatic
   uint64_t seed = 0x46533230ull;  // "FS20"
   fs_ctx* ctx = nullptr;
   int ctx_device = -1;
@@ -44,13 +49,21 @@ void fail_msg(const char* msg) {
 
 int ensure_context() {
   TraceState& st = state();
-  if (st.ctx && st.ctx_device == st.device) return 0;
+  if (st.ctx && st.ctx_device == st.device && !st.devices_changed) return 0;
   if (st.ctx) fs_destroy(st.ctx);
   st.ctx = nullptr;
   st.scene = nullptr;
   st.frame = nullptr;
   st.film_w = st.film_h = 0;
-  if (fs_create(&st.ctx, st.device, 0) != FS_OK) return fail("fs_create", nullptr);
+  st.devices_changed = false;
+  if (st.devices.size() > 1) {
+    // every GPU of the box behind the one TraceScene call, as the reference puts every core
+    // behind it (engine.cpp:261-274)
+    if (fs_create_multi(&st.ctx, st.devices.data(), (int)st.devices.size(), 0) != FS_OK)
+      return fail("fs_create_multi", nullptr);
+  } else if (fs_create(&st.ctx, st.device, 0) != FS_OK) {
+    return fail("fs_create", nullptr);
+  }
   st.ctx_device = st.device;
   return 0;
 }
@@ -148,7 +161,24 @@ const float32* DisplayFrame::GetDepthBuffer() { return impl_->depth.data(); }
 const uint64* DisplayFrame::GetMaterialIdBuffer() { return impl_->mat_id.data(); }
 
 // ---------------------------------------------------------------- tracing
-void SetTraceDevice(int device) { state().device = device; }
+void SetTraceDevice(int device) {
+  TraceState& st = state();
+  if (st.devices.size() > 1) st.devices_changed = true;
+  st.devices.clear();
+  st.device = device;
+}
+void SetTraceDevices(const int* devices, int n_devices) {
+  TraceState& st = state();
+  std::vector<int> ids(devices, devices + (n_devices > 0 ? n_devices : 0));
+  if (ids.empty()) ids.push_back(0);
+  if (ids != st.devices) st.devices_changed = true;
+  st.devices = ids;
+  st.device = ids[0];
+}
+int GetTraceDeviceCount() { return state().ctx ? fs_device_count(state().ctx) : (int)std::max<size_t>(1, state().devices.size()); }
+void SetTraceSharding(int mode) {
+  state().shard_flags = mode == 1 ? FS_TRACE_SHARD_SAMPLES : mode == 2 ? FS_TRACE_SHARD_TILES : 0;
+}
 void SetTraceSeed(uint64 seed) { state().seed = seed; }
 const char* LastTraceError() { return state().error; }
 
@@ -173,7 +203,7 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
     f->samples = 0;
   }
   fs_camera cam = to_pod(view);
-  if (fs_trace(st.ctx, &cam, f->samples, n_samples, 1, st.seed, FS_TRACE_DEFAULT) != FS_OK)
+  if (fs_trace(st.ctx, &cam, f->samples, n_samples, 1, st.seed, FS_TRACE_DEFAULT | st.shard_flags) != FS_OK)
     return fail("fs_trace", st.ctx);
   f->samples += n_samples;
   f->frame_count += n_samples;
@@ -305,6 +335,19 @@ int fs2h_scene_camera(void* s, int index, fs_camera* out) {
   *out = to_pod(c ? *c : def);  // default viewpoint of reference source/main.cpp:87-88
   return c ? 0 : 1;
 }
+// API-only content for generated scenes (FogMaterial cannot be written in a .scene file,
+// reference source/scene.cpp:285-303): a rotated cuboid of fog, through the mirrored C++ API.
+// v = position xyz, width, height, depth, rotation axis xyz, angle, colour rgb, density.
+int fs2h_scene_add_fog_cuboid(void* s, const float* v) {
+  base::Scene* scene = (base::Scene*)s;
+  base::CuboidObject* box =
+      scene->AddCuboidObject(base::vector3(v[0], v[1], v[2]), v[3], v[4], v[5]);
+  if (!box) return -1;
+  if (v[9] != 0.0f) box->Rotate(base::vector3(v[6], v[7], v[8]), v[9]);
+  box->SetMaterial(std::make_shared<base::FogMaterial>(base::vector3(v[10], v[11], v[12]), v[13]));
+  scene->Optimize();
+  return 0;
+}
 void* fs2h_frame_new(uint32_t w, uint32_t h) { return new base::DisplayFrame(w, h); }
 void fs2h_frame_free(void* f) { delete (base::DisplayFrame*)f; }
 void fs2h_frame_reset(void* f) { ((base::DisplayFrame*)f)->Reset(); }
@@ -330,6 +373,9 @@ float fs2h_trace_range(void* scene, const fs_camera* cam, void* frame, float x, 
   return base::TraceRange(from_pod(cam), (base::Scene*)scene, (base::DisplayFrame*)frame, x, y);
 }
 void fs2h_set_device(int device) { base::SetTraceDevice(device); }
+void fs2h_set_devices(const int* devices, int n) { base::SetTraceDevices(devices, n); }
+void fs2h_set_sharding(int mode) { base::SetTraceSharding(mode); }
+int fs2h_device_count() { return base::GetTraceDeviceCount(); }
 void fs2h_set_seed(uint64_t seed) { base::SetTraceSeed(seed); }
 // Mesh octrees are built by the CUDA library on `device` (-1: by the host builder).
 void fs2h_set_gpu_build(int device) { fs2h::gpu_build_device() = device; }

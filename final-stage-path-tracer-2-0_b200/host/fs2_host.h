@@ -260,6 +260,15 @@ float32 TraceRange(const Camera& viewer, Scene* scene, DisplayFrame* frame, floa
 int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 n_samples);
 // Selects the CUDA device used by TraceScene/TraceRange (default 0) and the seed.
 void SetTraceDevice(int device);
+// Puts several GPUs of the box behind TraceScene / TraceSamples (fs_create_multi): the scene is
+// replicated, every call's samples (or, with fewer samples than GPUs, interleaved pixel tiles)
+// are sharded across them and the film is combined on devices[0] before it is copied into the
+// DisplayFrame.  The GPU counterpart of the reference's fan-out over hardware_concurrency()
+// threads (engine.cpp:261-274).
+void SetTraceDevices(const int* devices, int n_devices);
+int GetTraceDeviceCount();
+// 0 automatic (sample indices; tiles when a call has fewer samples than GPUs), 1 samples, 2 tiles
+void SetTraceSharding(int mode);
 void SetTraceSeed(uint64 seed);
 const char* LastTraceError();
 // Film checkpoint / resume (headless replacement of keeping the window open): the accumulation

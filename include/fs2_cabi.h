@@ -199,6 +199,9 @@ typedef struct fs_camera {
 #define FS_TRACE_LBVH_LANE 128 /* megakernel; per-leaf 4-wide BVH walked by free-running lanes (nested loops) */
 #define FS_TRACE_MEGAKERNEL 256 /* megakernel; warp-synchronous phase machine over the leaf BVH (one launch,
                                  * a pixel's samples are summed in order: bit-reproducible films) */
+#define FS_TRACE_SHARD_TILES 512    /* multi-device context: interleaved 16x8-pixel tiles per device */
+#define FS_TRACE_SHARD_SAMPLES 1024 /* multi-device context: sample indices per device (the default
+                                     * whenever there are at least as many samples as devices) */
 /* default (none of the four megakernel flags): the wavefront pipeline.  Its traversal kernel is
  * the same phase machine over the per-leaf 4-wide BVH built by fs_scene_upload; every path has
  * the RNG stream and arithmetic of the megakernels, but a pixel's samples reach the film through
@@ -226,6 +229,16 @@ typedef struct fs_ctx fs_ctx;
 /* Lifetime.  `device` is a CUDA ordinal; the context uses that device's
  * primary context, so pointers interoperate with other runtime users. */
 int fs_create(fs_ctx** out, int device, int flags);
+/* One context over several devices of the box: what the reference's thread fan-out over every
+ * core (source/engine.cpp:261-274) becomes on an 8-GPU machine.  The scene is replicated by
+ * fs_scene_upload, fs_trace shards the requested samples (or, with fewer samples than devices,
+ * interleaved pixel tiles) across the devices — one host thread each — and combines the films on
+ * device_ids[0] with a kernel that reads the other devices' films over NVLink peer mappings, in
+ * device order (deterministic); every other call acts on the film of device_ids[0].  Per-sample
+ * random streams depend only on (seed, pixel, sample index), so the result is the single-device
+ * sample set.  Every entry point below accepts such a context. */
+int fs_create_multi(fs_ctx** out, const int* device_ids, int n_devices, int flags);
+int fs_device_count(const fs_ctx* ctx); /* 1 for fs_create contexts */
 int fs_destroy(fs_ctx* ctx);
 const char* fs_last_error(const fs_ctx* ctx); /* ctx may be NULL: global last error */
 int fs_abi_version(void);
@@ -268,10 +281,17 @@ int fs_trace(fs_ctx* ctx, const fs_camera* cam, uint32_t first_sample,
 int fs_film_read(fs_ctx* ctx, float* mean_rgb, uint32_t* count, uint8_t* rgb8,
                  float* normal, float* depth, uint64_t* mat_id);
 
-/* Device views for the multi-GPU reduce: sum = float4 per pixel (rgb sum,
- * w = sample count as float).  After an external reduce call fs_film_resolve
+/* Device views for a multi-process reduce (one process per GPU, e.g. NCCL): sum = float4 per
+ * pixel (rgb sum, w = sample count as float).  After an external reduce call fs_film_resolve
  * to refresh mean/rgb8. */
 int fs_film_device(fs_ctx* ctx, void** sum_rgba, size_t* n_floats);
+/* ... and the aux planes (float4 normal xyz + depth, u32 material id per pixel): with tile
+ * sharding every pixel is non-zero on exactly one rank, so summing them gathers them. */
+int fs_film_device_aux(fs_ctx* ctx, void** aux_xyzd, void** mat_id_u32, size_t* n_pixels);
+/* Multi-process tile sharding: this context renders only the 16x8-pixel tiles (tx, ty) with
+ * (tx + ty) mod world == rank (all samples of them); world = 1 restores the whole image.
+ * Default pipeline only. */
+int fs_set_tile_shard(fs_ctx* ctx, int rank, int world);
 
 /* Film checkpoint / resume: copies the accumulation film (4 floats per pixel: rgb sum, sample
  * count) to / from a host buffer of width*height*4 floats.  After fs_film_load the resolved

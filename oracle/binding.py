@@ -145,7 +145,7 @@ def have_ref():
 
 def run_ref(scene_path, width, height, flatten=None, firsthit=None, render=None, frames=1,
             threads=1, realclock=False, aperture=None, focal=None, time_only=False, cores=None,
-            timeout=3600):
+            timeout=3600, fog=None):
     """Runs oracle/_ref/fs2_ref; returns the parsed FS2REF json summary (if rendering)."""
     cmd = [REF_BIN, scene_path, "--width", str(width), "--height", str(height)]
     if flatten:
@@ -163,6 +163,8 @@ def run_ref(scene_path, width, height, flatten=None, firsthit=None, render=None,
         cmd += ["--aperture", str(aperture)]
     if focal is not None:
         cmd += ["--focal", str(focal)]
+    if fog is not None:  # 14 floats: a FogMaterial cuboid added through the reference's C++ API
+        cmd += ["--fog", ",".join("%.9g" % v for v in fog)]
     if cores:
         cmd = ["taskset", "-c", "0-%d" % (cores - 1)] + cmd
     r = subprocess.run(cmd, capture_output=True, text=True, timeout=timeout)

@@ -532,6 +532,8 @@ int main(int argc, char** argv) {
              *json_path = nullptr;
   bool do_render = false, have_aperture = false, have_focal = false, fast = false;
   float aperture = 0, focal = 0;
+  float fog[14];  // --fog: position, size, rotation axis + angle, colour, density
+  bool have_fog = false;
   const char* paths_path = nullptr;
   uint32_t path_samples = 1, path_first = 0, path_stride = 1;
   uint64_t path_seed = 1;
@@ -552,6 +554,12 @@ int main(int argc, char** argv) {
     else if (a == "--focal") { focal = (float)atof(next()); have_focal = true; }
     else if (a == "--json") json_path = next();
     else if (a == "--fast") fast = true;  // Camera::fast_render_enabled (engine.cpp:68-70)
+    else if (a == "--fog") {  // 14 comma-separated floats: a FogMaterial cuboid added through the API
+      have_fog = sscanf(next(), "%f,%f,%f,%f,%f,%f,%f,%f,%f,%f,%f,%f,%f,%f", fog, fog + 1, fog + 2, fog + 3,
+                        fog + 4, fog + 5, fog + 6, fog + 7, fog + 8, fog + 9, fog + 10, fog + 11, fog + 12,
+                        fog + 13) == 14;
+      if (!have_fog) { usage(); return 64; }
+    }
     else if (a == "--paths") paths_path = next();
     else if (a == "--samples") path_samples = (uint32_t)atoi(next());
     else if (a == "--first-sample") path_first = (uint32_t)atoi(next());
@@ -570,6 +578,12 @@ int main(int argc, char** argv) {
     build_api_scene(&scene, scene_path.size() > 5 ? scene_path.c_str() + 5 : "");
   } else if (!scene.LoadScene(scene_path)) {
     return 1;
+  }
+  if (have_fog) {  // FogMaterial is API-only (scene.cpp:285-303): same call sequence as the host mirror
+    CuboidObject* box = scene.AddCuboidObject(vector3(fog[0], fog[1], fog[2]), fog[3], fog[4], fog[5]);
+    if (fog[9] != 0.0f) box->Rotate(vector3(fog[6], fog[7], fog[8]), fog[9]);
+    box->SetMaterial(std::make_shared<FogMaterial>(vector3(fog[10], fog[11], fog[12]), fog[13]));
+    scene.Optimize();
   }
   InitializeMaterials();
 

@@ -1,4 +1,5 @@
-"""Minimal OpenEXR 2 scan-line writer for the reader tests (tests/test_exr_reader.py): single
+"""Minimal OpenEXR 2 scan-line writer for generated scene assets (float environment maps,
+scenes/gen_scenes.py) and the reader tests (tests/test_exr_reader.py): single
 part, HALF or FLOAT channels, compression NONE / RLE / ZIPS / ZIP, either line order, any data
 window origin.  Follows the published file layout (magic 20000630, attribute list, offset
 table, chunks of { y, size, data }; ZIP / RLE data = even/odd byte split, byte delta, deflate or

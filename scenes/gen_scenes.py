@@ -319,11 +319,29 @@ def scene_mesh(outdir, nu, nv, name, aperture=0.0, knot=False):
     return s
 
 
-def scene_glass(outdir, aperture=0.0, sky_size=(512, 256)):
+def sky_texture_exr(path, w=1024, h=512):
+    """The same analytic sky as a float .exr (HALF, ZIP): a sun of radiance ~40 that an 8-bit
+    .bmp would clip ('float env texture written as .exr')."""
+    from exr_write import write_exr
+    v, u = np.mgrid[0:h, 0:w]
+    el = v / (h - 1.0)
+    img = np.zeros((h, w, 3), np.float64)
+    img[..., 0] = (70 + 110 * el) / 255.0
+    img[..., 1] = (110 + 100 * el) / 255.0
+    img[..., 2] = (200 + 40 * el) / 255.0
+    du = (u - 0.62 * w) / w
+    dv = (v - 0.30 * h) / h
+    sun = np.exp(-(du * du * 4 + dv * dv) * 900.0)
+    img += sun[..., None] * 40.0
+    img = img.astype(np.float16)
+    write_exr(path, {"R": img[..., 0], "G": img[..., 1], "B": img[..., 2]}, comp="zip")
+
+
+def scene_glass(outdir, aperture=0.0, sky_size=(512, 256), exr_sky=False):
     """Config 3: glass / frosted glass / liquid primitives, ceramic, env-map sky."""
-    sky = os.path.join(outdir, "sky_%dx%d.bmp" % sky_size)
+    sky = os.path.join(outdir, "sky_%dx%d.%s" % (sky_size + ("exr" if exr_sky else "bmp",)))
     if not os.path.exists(sky):
-        sky_texture(sky, *sky_size)
+        (sky_texture_exr if exr_sky else sky_texture)(sky, *sky_size)
     s = "# fs2-b200 glass + liquid scene under an environment texture (BASELINE config 3)\n"
     s += common_materials(outdir)
     s += material("env_mat", emission=(1.0, 1.0, 1.0), texture_scale=1.0, texture=sky)
@@ -565,6 +583,9 @@ SCENES = {
     "glass": lambda d: scene_glass(d),
     "glass_small": lambda d: scene_glass(d, sky_size=(64, 32)),
     "glass_dof": lambda d: scene_glass(d, aperture=1.5),
+    # config 3 as SURVEY 8(d) states it: float .exr environment; bench.py adds the fog cuboid
+    # through the C++ API (FogMaterial is not expressible in the .scene grammar, App. A13)
+    "glass3": lambda d: scene_glass(d, aperture=1.5, sky_size=(1024, 512), exr_sky=True),
     "grid_tiny": lambda d: scene_grid(d, 24, 12, "gtiny", aperture=0.0),
     "grid_small": lambda d: scene_grid(d, 64, 32, "gsmall"),
     "grid4m": lambda d: scene_grid(d, 2048, 1024, "g4m"),

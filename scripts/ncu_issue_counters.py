@@ -2,7 +2,8 @@
 """Extracts from an `ncu --set full` report the counters bench.py's roofline line is built from
 and writes them as JSON (committed under profiles/, read back by bench.py):
 
-    python scripts/ncu_issue_counters.py report.ncu-rep [kernel-substring] > profiles/rN_issue_counters.json
+    python scripts/ncu_issue_counters.py report.ncu-rep [kernel-substring] [--scene NAME]
+        [--shade-report shade.ncu-rep --rays-per-launch N] > profiles/rN_issue_counters.json
 
   issue_slot_busy_pct   sm__inst_issued.avg.pct_of_peak_sustained_active ("Issue Slots Busy")
   active_threads        smsp__thread_inst_executed_per_inst_executed.ratio
@@ -13,7 +14,9 @@ and writes them as JSON (committed under profiles/, read back by bench.py):
                         is anywhere near its peak, see the dram_* and fp32 fields)
 plus occupancy, cache hit rates, DRAM bytes and duration of the profiled launches (averaged over
 the launches in the report that match the kernel substring), and a hash of the kernel sources
-the report belongs to.
+the report belongs to.  With --shade-report and --rays-per-launch (captures of full waves of a
+known size, FS2_TUNE pool) it also writes dram_bytes_per_segment = (DRAM bytes of one k_wf_trace
++ one k_wf_shade launch) / rays: the measured HBM traffic per ray segment bench.py scales.
 """
 import csv
 import hashlib
@@ -62,9 +65,7 @@ def to_unit(value, unit, want):
     return v
 
 
-def main():
-    rep = sys.argv[1]
-    pattern = sys.argv[2] if len(sys.argv) > 2 else "k_wf_trace"
+def load(rep, pattern):
     txt = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
     rows = list(csv.reader(io.StringIO(txt)))
     hdr, units, data = rows[0], rows[1], rows[2:]
@@ -73,8 +74,30 @@ def main():
     picked = [r for r in data if name_col is None or pattern in r[name_col]]
     if not picked:
         raise SystemExit("no launch of %r in %s" % (pattern, rep))
+    return col, units, picked, name_col
+
+
+def dram_mb(rep, pattern):
+    col, units, picked, _ = load(rep, pattern)
+    tot = []
+    for r in picked:
+        tot.append(sum(to_unit(r[col[m]], units[col[m]], "mb") for m in ("dram__bytes_read.sum", "dram__bytes_write.sum")))
+    return sum(tot) / len(tot)
+
+
+def main():
+    argv = sys.argv[1:]
+    opts = {}
+    for flag in ("--scene", "--shade-report", "--rays-per-launch"):
+        if flag in argv:
+            i = argv.index(flag)
+            opts[flag] = argv[i + 1]
+            del argv[i:i + 2]
+    rep = argv[0]
+    pattern = argv[1] if len(argv) > 1 else "k_wf_trace"
+    col, units, picked, name_col = load(rep, pattern)
     out = {"kernel": picked[0][name_col] if name_col is not None else pattern, "launches": len(picked),
-           "report": os.path.basename(rep), "csrc_sha16": csrc_hash()}
+           "report": os.path.basename(rep), "csrc_sha16": csrc_hash(), "scene": opts.get("--scene", "mesh100k")}
     for key, metric in FIELDS.items():
         if metric not in col:
             out[key] = None
@@ -89,6 +112,13 @@ def main():
         out[key] = sum(vals) / len(vals) if vals else None
     if out["issue_slot_busy_pct"] is not None and out["nonpred_threads"] is not None:
         out["lane_issue_frac"] = out["issue_slot_busy_pct"] / 100.0 * out["nonpred_threads"] / 32.0
+    if "--shade-report" in opts and "--rays-per-launch" in opts:
+        rays = float(opts["--rays-per-launch"])
+        shade = dram_mb(opts["--shade-report"], "k_wf_shade")
+        trace = (out["dram_read_mb"] or 0.0) + (out["dram_write_mb"] or 0.0)
+        out["shade_dram_mb"] = shade
+        out["rays_per_launch"] = rays
+        out["dram_bytes_per_segment"] = (shade + trace) * 1e6 / rays
     json.dump(out, sys.stdout, indent=1, sort_keys=True)
     sys.stdout.write("\n")
 

@@ -15,7 +15,7 @@ material id) of the unmodified reference fed the CUDA path's random streams
 (oracle/_ref/fs2_ref_ctr, oracle/ref/ctr_rng.cpp) for PATH_SAMPLES sample indices, plus one
 sample with Camera::fast_render_enabled (engine.cpp:68-70).
 In tests/golden/exr_textures.npz: small .exr files (HALF / FLOAT x NONE / RLE / ZIPS / ZIP,
-written by tests/exr_write.py) and the texel arrays the reference's own loader — tinyexr's
+written by scenes/exr_write.py) and the texel arrays the reference's own loader — tinyexr's
 LoadEXR behind DiffuseMaterial::LoadDiffuseTexture, source/material.cpp:70-92 — made of them.
 The GPU box has no /root/reference: tests there only read these files.
 """
@@ -65,8 +65,7 @@ def dump_paths(scene_path, tmp, name, samples, fast):
 def exr_goldens(tmp):
     """Eight small .exr files through the reference's own loader (one scene, one textured
     material per file; the flattened scene's texel array is what LoadEXR produced)."""
-    sys.path.insert(0, os.path.join(REPO, "tests"))
-    from exr_write import write_exr
+    from exr_write import write_exr  # scenes/exr_write.py
     rng = np.random.default_rng(11)
     out = {}
     text = ""

@@ -1,5 +1,5 @@
 """the .exr texture reader of the host side (host/fs2_exr.cpp) against
-files written by tests/exr_write.py from the published OpenEXR layout.  The reference reads .exr
+files written by scenes/exr_write.py from the published OpenEXR layout.  The reference reads .exr
 through tinyexr's LoadEXR (source/material.cpp:70-92), a third-party header that is not in
 /root/reference, so the format specification is the anchor: values must come back exactly
 (HALF -> float conversion is exact), rows top to bottom, R / G / B picked by name."""
@@ -137,7 +137,7 @@ def test_exr_writer_round_trips_through_the_reader(tmp_path):
 
 def test_exr_against_an_independent_codec(tmp_path):
     """Cross-check with the OpenEXR library inside OpenCV (when the image has it): files of
-    tests/exr_write.py and of save_exr read by OpenCV, OpenCV's own file read by load_exr."""
+    scenes/exr_write.py and of save_exr read by OpenCV, OpenCV's own file read by load_exr."""
     os.environ["OPENCV_IO_ENABLE_OPENEXR"] = "1"
     cv2 = pytest.importorskip("cv2")
     img = _image(37, 29, np.float32, 11)

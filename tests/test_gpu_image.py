@@ -65,8 +65,9 @@ def test_converged_image_matches_oracle(ctx, name):
            "regions": {}}
     assert max(e1, e2) <= min(FLOOR_FACTOR * floor + SLACK, floor + 0.02)
     # per first-hit material region (a wrong constant in one material only moves its pixels):
-    # relative RMSE against the same gate, and the region's mean radiance within 3 standard
-    # errors of the oracle-vs-oracle difference (+ 0.5 %)
+    # relative RMSE against the same gate, and the region's mean radiance within 5 standard
+    # errors (+ 0.3 %): one run's per-pixel relative noise is floor / sqrt 2, the mean of n pixels
+    # of the GPU image against the average of the two oracle images has sqrt(1.5 / n) of it
     ids = binding.first_hit(g.scene, g.cam, w, h)["mat_id"]
     both = 0.5 * (a.astype(np.float64) + b.astype(np.float64))
     for mid in np.unique(ids):
@@ -76,11 +77,12 @@ def test_converged_image_matches_oracle(ctx, name):
         rf = rel_rmse(a[m], b[m])
         re = max(rel_rmse(film["mean"][m], a[m]), rel_rmse(film["mean"][m], b[m]))
         mean_gpu, mean_or = float(film["mean"][m].mean()), float(both[m].mean())
-        spread = abs(float(a[m].mean()) - float(b[m].mean()))
+        sigma = rf / np.sqrt(2.0) * np.sqrt(1.5 / int(m.sum()))
         rec["regions"][str(int(mid))] = {"pixels": int(m.sum()), "gpu_vs_oracle": re, "oracle_floor": rf,
-                                         "mean_gpu": mean_gpu, "mean_oracle": mean_or}
+                                         "mean_gpu": mean_gpu, "mean_oracle": mean_or,
+                                         "mean_sigma_rel": float(sigma)}
         assert re <= FLOOR_FACTOR * rf + 2 * SLACK, (name, int(mid), re, rf)
-        assert abs(mean_gpu - mean_or) <= 3.0 * spread + 0.005 * mean_or + 1e-3, (name, int(mid))
+        assert abs(mean_gpu - mean_or) <= (5.0 * sigma + 0.003) * mean_or + 1e-3, (name, int(mid), mean_gpu, mean_or)
     _report(name, rec)
     # mean brightness must agree much tighter than per-pixel noise (bias check)
     assert abs(film["mean"].mean() - a.mean()) <= 0.01 * a.mean() + 1e-3
