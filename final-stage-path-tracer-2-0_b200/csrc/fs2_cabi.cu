@@ -198,8 +198,8 @@ int validate_scene(fs_ctx* ctx, const fs_scene_desc* s) {
       (s->n_faces && !s->faces) || (s->n_objects && !s->objects) || !s->materials ||
       (s->n_textures && (!s->textures || !s->texels)) || (s->n_scene_refs && !s->scene_refs))
     return fail(ctx, FS_E_INVALID, "null array with non-zero count");
-  if (s->n_nodes >= (1u << FS2_PH_NODE_BITS))
-    return fail(ctx, FS_E_INVALID, "more than 2^%d octree nodes", FS2_PH_NODE_BITS);
+  if (s->n_nodes >= (1u << FS2_NODE_INDEX_BITS))
+    return fail(ctx, FS_E_INVALID, "more than 2^%d octree nodes", FS2_NODE_INDEX_BITS);
   if (s->scene_root >= 0 && (uint32_t)s->scene_root >= s->n_nodes)
     return fail(ctx, FS_E_INVALID, "scene_root %d out of range", s->scene_root);
   for (uint32_t i = 0; i < s->n_nodes; i++) {
@@ -462,13 +462,37 @@ std::vector<fs_ctx*> all_contexts(fs_ctx* ctx) {
   return all;
 }
 
+// Device copy of the node array: the `first` word of every internal node gets the occupancy of
+// its eight children in its top byte (bit c set = child c is internal or a non-empty leaf), so
+// the traversal kernel answers visits to empty leaves from the parent (fs2_phase.cuh).  Node
+// indices stay below 2^FS2_NODE_INDEX_BITS (validate_scene).  The ABI's fs_node is unchanged.
+std::vector<fs_node> tag_nodes(const fs_scene_desc* s) {
+  std::vector<fs_node> t(s->nodes, s->nodes + s->n_nodes);
+  for (uint32_t i = 0; i < s->n_nodes; i++) {
+    if (t[i].count != FS_NODE_INTERNAL) continue;
+    uint32_t mask = 0;
+    for (uint32_t c = 0; c < 8; c++)
+      if (s->nodes[t[i].first + c].count != 0u) mask |= 1u << c;
+    t[i].first |= mask << FS2_NODE_INDEX_BITS;
+  }
+  return t;
+}
+void untag_nodes(std::vector<fs_node>& t) {
+  for (fs_node& n : t)
+    if (n.count == FS_NODE_INTERNAL) n.first &= (1u << FS2_NODE_INDEX_BITS) - 1u;
+}
+
 // One device's copy of the (validated) scene.
 int scene_upload_one(fs_ctx* ctx, const fs_scene_desc* s, const std::vector<float>& lut4,
                      const LbvhHost& lb) {
   int rc;
   if ((rc = set_device(ctx))) return rc;
   ctx->have_scene = false;
-  if ((rc = dev_upload(ctx, &ctx->nodes, s->nodes, (size_t)s->n_nodes * sizeof(fs_node)))) return rc;
+  {
+    std::vector<fs_node> tagged = tag_nodes(s);
+    if ((rc = dev_upload(ctx, &ctx->nodes, tagged.data(), tagged.size() * sizeof(fs_node)))) return rc;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `tagged` is pageable and dies here
+  }
   if ((rc = dev_upload(ctx, &ctx->scene_refs, s->scene_refs, (size_t)s->n_scene_refs * 4))) return rc;
   if ((rc = dev_upload(ctx, &ctx->tri_plane, s->tri_plane, (size_t)s->n_tris * 16))) return rc;
   if ((rc = dev_upload(ctx, &ctx->tri_aux, s->tri_aux, (size_t)s->n_tris * sizeof(fs_tri_aux)))) return rc;
@@ -518,6 +542,7 @@ int ensure_lbvh_for_camera(fs_ctx* ctx, const fs_camera* cam) {
   std::vector<fs_object> objects(ctx->n_objects);
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   CUDA_TRY(ctx, cudaMemcpy(nodes.data(), ctx->nodes.p, nodes.size() * sizeof(fs_node), cudaMemcpyDeviceToHost));
+  untag_nodes(nodes);
   CUDA_TRY(ctx, cudaMemcpy(plane.data(), ctx->tri_plane.p, plane.size() * 4, cudaMemcpyDeviceToHost));
   CUDA_TRY(ctx, cudaMemcpy(aux.data(), ctx->tri_aux.p, aux.size() * sizeof(fs_tri_aux), cudaMemcpyDeviceToHost));
   CUDA_TRY(ctx, cudaMemcpy(objects.data(), ctx->objects.p, objects.size() * sizeof(fs_object), cudaMemcpyDeviceToHost));

@@ -375,7 +375,7 @@ k_trace_phase(DScene S, CamBasis cam, Film film, TraceParams tp,
     FS2_PHASE(PH_ENTER, 2, ph_enter<STATS>(S, w, ps.ray, sm, c))
     FS2_PHASE(PH_LB_NODE, 2, ph_lb_node<STATS>(S, w, ps.ray, q, sm, c))
     FS2_PHASE(PH_LB_TRIS, 2, ph_lb_tris<STATS>(S, w, ps.ray, sm, c))
-    FS2_PHASE(PH_RETURN, 4, ph_return(S, w, ps.ray, sm))
+    FS2_PHASE(PH_RETURN, 4, ph_return<STATS>(S, w, ps.ray, sm, c))
     unsigned m_shade = __ballot_sync(0xFFFFFFFFu, w.st == PH_SHADE);
     unsigned m_busy = __ballot_sync(0xFFFFFFFFu, w.st != PH_SHADE && w.st != PH_IDLE);
     if (m_shade && (__popc(m_shade) >= FS2_PH_SHADE_BATCH || !m_busy)) {

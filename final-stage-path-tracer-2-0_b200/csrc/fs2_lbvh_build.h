@@ -23,6 +23,13 @@ namespace fs2 {
 
 // Leaves with fewer triangles than this are scanned directly (one node, no tree).
 #define FS2_LBVH_MAX_LEVELS 7  // 4^(7+1) = 65 536 triangles per octree leaf
+#ifndef FS2_LBVH_SAH_MAX
+#define FS2_LBVH_SAH_MAX 4096u  // order 2: ranges up to this size try all three cut axes
+#endif
+#ifndef FS2_LBVH_ORDER
+#define FS2_LBVH_ORDER 3  // leaf build: 0 Morton curve, 1 median cuts on the longest axis, 2 median cuts on the
+                          // axis with the smallest half areas (implicit complete trees), 3 surface-area cuts
+#endif
 
 // 128-byte node: boxes of its 4 children as SoA, then the link word.
 struct LbNode {
@@ -269,6 +276,8 @@ inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out
     }
     cb.add(&cen[3 * (size_t)i]);
   }
+#if FS2_LBVH_ORDER == 0
+  // Morton order of the record centres (10 bits per axis)
   float scale[3];
   for (int k = 0; k < 3; k++) {
     float e = cb.hi[k] - cb.lo[k];
@@ -284,6 +293,83 @@ inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out
     keys[i] = ((uint64_t)code << 32) | i;
   }
   std::sort(keys.begin(), keys.end());
+#else
+  // Median-split order: the implicit tree's node i of level l covers the records
+  // [4^(l+1) i, 4^(l+1) (i+1)), so the permutation is chosen top down — the range of a node is cut
+  // at its children's block boundaries along the longest axis of its centres (two binary cuts
+  // per node) — and every aligned block ends up a compact patch of the surface.  Measured against
+  // the Morton order on config 2: see DESIGN.md 4.3.
+  {
+    std::vector<uint32_t> perm(n);
+    for (uint32_t i = 0; i < n; i++) perm[i] = i;
+    auto cut = [&](uint32_t lo, uint32_t mid, uint32_t hi) {
+      if (mid <= lo || mid >= hi) return;
+      float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+      for (uint32_t i = lo; i < hi; i++)
+        for (int k = 0; k < 3; k++) {
+          float v = cen[3 * (size_t)perm[i] + k];
+          mn[k] = fminf(mn[k], v);
+          mx[k] = fmaxf(mx[k], v);
+        }
+      auto less_on = [&](int ax) {
+        return [&cen, ax](uint32_t a, uint32_t b) {
+          float va = cen[3 * (size_t)a + ax], vb = cen[3 * (size_t)b + ax];
+          return va < vb || (va == vb && a < b);
+        };
+      };
+      int ax = 0;
+      if (mx[1] - mn[1] > mx[ax] - mn[ax]) ax = 1;
+      if (mx[2] - mn[2] > mx[ax] - mn[ax]) ax = 2;
+#if FS2_LBVH_ORDER == 2
+      // try the three axes, keep the cut whose halves have the smallest total surface area
+      if (hi - lo <= FS2_LBVH_SAH_MAX) {
+        double best = INFINITY;
+        std::vector<uint32_t> tmp(perm.begin() + lo, perm.begin() + hi), keep;
+        for (int a = 0; a < 3; a++) {
+          std::vector<uint32_t> t2 = tmp;
+          std::nth_element(t2.begin(), t2.begin() + (mid - lo), t2.end(), less_on(a));
+          Box3 l, r;
+          l.reset();
+          r.reset();
+          for (uint32_t i = 0; i < t2.size(); i++) (i < mid - lo ? l : r).add(boxes[t2[i]]);
+          auto area = [](const Box3& b) {
+            double x = (double)b.hi[0] - b.lo[0], y = (double)b.hi[1] - b.lo[1], z = (double)b.hi[2] - b.lo[2];
+            double v = x * y + y * z + z * x;
+            return v == v && !isinf(v) ? v : 1e300;
+          };
+          double cost = area(l) * (mid - lo) + area(r) * (hi - mid);
+          if (cost < best) {
+            best = cost;
+            keep.swap(t2);
+          }
+        }
+        std::copy(keep.begin(), keep.end(), perm.begin() + lo);
+        return;
+      }
+#endif
+      std::nth_element(perm.begin() + lo, perm.begin() + mid, perm.begin() + hi, less_on(ax));
+    };
+    uint32_t top = 4;  // records under one child of the root
+    while ((uint64_t)4 * top < n) top *= 4;
+    struct Range {
+      uint32_t lo, hi, block;
+    };
+    std::vector<Range> todo;
+    todo.push_back({0u, n, top});
+    while (!todo.empty()) {
+      Range r = todo.back();
+      todo.pop_back();
+      const uint32_t b = r.block;
+      cut(r.lo, r.lo + 2 * b, r.hi);
+      cut(r.lo, r.lo + b, r.lo + 2 * b < r.hi ? r.lo + 2 * b : r.hi);
+      if (r.lo + 2 * b < r.hi) cut(r.lo + 2 * b, r.lo + 3 * b, r.hi);
+      if (b > 4)
+        for (uint32_t c = 0; c < 4 && r.lo + c * b < r.hi; c++)
+          todo.push_back({r.lo + c * b, r.lo + (c + 1) * b < r.hi ? r.lo + (c + 1) * b : r.hi, b / 4});
+    }
+    for (uint32_t i = 0; i < n; i++) keys[i] = perm[i];
+  }
+#endif
   std::vector<Box3> cur(n);
   for (uint32_t i = 0; i < n; i++) {
     uint32_t src = (uint32_t)(keys[i] & 0xFFFFFFFFu);
@@ -352,6 +438,197 @@ inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out
   }
 }
 
+
+// ------------------------------------------------------------------ order 3: surface-area build
+// Top-down build with explicit child links (the kernels only ever follow LbNode::child, so the
+// tree need not be the implicit complete one): every inner node cuts its records twice — first
+// in two, then each half in two — at the position and axis with the smallest
+// area(L) * groups(L) + area(R) * groups(R) (full sweep over the three centre orders), subject to
+// the depth budget: a node with `levels` inner levels left below it holds at most 16 * 4^levels
+// records, so the walk's stack bound (3 pending siblings per inner level, FS2_PH_LB_STACK) holds
+// for any shape.  Ranges above FS2_LBVH_SAH_MAX are cut at the median of the longest axis.
+struct SahLeafBuilder {
+  const std::vector<Box3>& boxes;
+  const std::vector<float>& cen;
+  std::vector<uint32_t>& perm;   // positions -> record (local index)
+  std::vector<LbNode>& nodes;    // local node array, root = 0, child links local
+  uint32_t first;                // first record of the leaf in the permuted arrays
+  std::vector<uint32_t> tmp, keep;
+  std::vector<double> rarea;
+
+  static double area(const Box3& b) {
+    double x = (double)b.hi[0] - b.lo[0], y = (double)b.hi[1] - b.lo[1], z = (double)b.hi[2] - b.lo[2];
+    double v = x * y + y * z + z * x;
+    return (v == v && !isinf(v)) ? v : 1.0e300;
+  }
+  Box3 range_box(uint32_t lo, uint32_t hi) const {
+    Box3 b;
+    b.reset();
+    for (uint32_t i = lo; i < hi; i++) b.add(boxes[perm[i]]);
+    return b;
+  }
+  // Cuts perm[lo, hi) into [lo, mid) and [mid, hi) with kmin <= mid - lo <= kmax (and both sides
+  // non-empty); `step` restricts the left size to multiples of it (group alignment).
+  uint32_t split(uint32_t lo, uint32_t hi, uint32_t kmin, uint32_t kmax, uint32_t step) {
+    const uint32_t n = hi - lo;
+    if (kmin < 1) kmin = 1;
+    if (kmax > n - 1) kmax = n - 1;
+    if (step > 1) {
+      kmin = (kmin + step - 1) / step * step;
+      kmax = kmax / step * step;
+    }
+    if (kmin > kmax) return lo + (n + 1) / 2;  // cannot happen for feasible budgets
+    auto less_on = [this](int ax) {
+      return [this, ax](uint32_t a, uint32_t b) {
+        float va = cen[3 * (size_t)a + ax], vb = cen[3 * (size_t)b + ax];
+        return va < vb || (va == vb && a < b);
+      };
+    };
+    if (n > FS2_LBVH_SAH_MAX) {
+      float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
+      for (uint32_t i = lo; i < hi; i++)
+        for (int k = 0; k < 3; k++) {
+          float v = cen[3 * (size_t)perm[i] + k];
+          mn[k] = fminf(mn[k], v);
+          mx[k] = fmaxf(mx[k], v);
+        }
+      int ax = 0;
+      if (mx[1] - mn[1] > mx[ax] - mn[ax]) ax = 1;
+      if (mx[2] - mn[2] > mx[ax] - mn[ax]) ax = 2;
+      uint32_t k = (n / 2 + step - 1) / step * step;
+      k = k < kmin ? kmin : k > kmax ? kmax : k;
+      std::nth_element(perm.begin() + lo, perm.begin() + lo + k, perm.begin() + hi, less_on(ax));
+      return lo + k;
+    }
+    double best = INFINITY;
+    uint32_t best_k = kmin;
+    tmp.assign(perm.begin() + lo, perm.begin() + hi);
+    rarea.resize(n + 1);
+    for (int ax = 0; ax < 3; ax++) {
+      std::sort(tmp.begin(), tmp.end(), less_on(ax));
+      Box3 b;
+      b.reset();
+      for (uint32_t i = n; i-- > 0;) {
+        b.add(boxes[tmp[i]]);
+        rarea[i] = area(b);
+      }
+      b.reset();
+      for (uint32_t k = 1; k <= kmax; k++) {
+        b.add(boxes[tmp[k - 1]]);
+        if (k < kmin || (step > 1 && k % step)) continue;
+        double cost = area(b) * ((k + 3) / 4) + rarea[k] * ((n - k + 3) / 4);
+        if (cost < best) {
+          best = cost;
+          best_k = k;
+          keep = tmp;
+        }
+      }
+    }
+    if (best < INFINITY) std::copy(keep.begin(), keep.end(), perm.begin() + lo);
+    return lo + best_k;
+  }
+  // orders the <= 16 records of a quad-level node into groups of four
+  void split_groups(uint32_t lo, uint32_t hi) {
+    if (hi - lo <= 4) return;
+    uint32_t mid = split(lo, hi, 4, hi - lo - 1, 4);
+    split_groups(lo, mid);
+    split_groups(mid, hi);
+  }
+  static uint64_t cap(int levels) { return (uint64_t)16 << (2 * levels); }
+
+  void build(uint32_t self, uint32_t lo, uint32_t hi, int levels) {
+    const uint32_t n = hi - lo;
+    LbNode nd;
+    memset(&nd, 0, sizeof nd);
+    for (int c = 0; c < 4; c++) {
+      nd.lox[c] = nd.loy[c] = nd.loz[c] = INFINITY;
+      nd.hix[c] = nd.hiy[c] = nd.hiz[c] = INFINITY;
+    }
+    auto set_box = [&](int c, const Box3& b) {
+      nd.lox[c] = b.lo[0];
+      nd.loy[c] = b.lo[1];
+      nd.loz[c] = b.lo[2];
+      nd.hix[c] = b.hi[0];
+      nd.hiy[c] = b.hi[1];
+      nd.hiz[c] = b.hi[2];
+    };
+    if (n <= 16) {
+      split_groups(lo, hi);
+      nd.kind = 1;
+      nd.child = first + lo;
+      nd.count = n;
+      for (uint32_t g = 0; 4 * g < n; g++) set_box((int)g, range_box(lo + 4 * g, lo + 4 * g + 4 < hi ? lo + 4 * g + 4 : hi));
+      nodes[self] = nd;
+      return;
+    }
+    const uint64_t cc = cap(levels - 1);  // most records a child may hold
+    auto lim = [](uint64_t v) { return (uint32_t)(v > 0xFFFFFFFFull ? 0xFFFFFFFFull : v); };
+    // first cut: both halves must fit two children
+    uint32_t mid = split(lo, hi, n > 2 * cc ? lim(n - 2 * cc) : 1, lim(2 * cc), 1);
+    uint32_t r[5] = {lo, lo, mid, mid, hi};
+    auto half = [&](uint32_t a, uint32_t b, uint32_t& m) {
+      uint32_t h = b - a;
+      if (h < 2) {
+        m = b;  // one child only
+        return;
+      }
+      m = split(a, b, h > cc ? lim(h - cc) : 1, lim(cc), 1);
+    };
+    half(lo, mid, r[1]);
+    half(mid, hi, r[3]);
+    // children: [r0,r1) [r1,r2) [r2,r3) [r3,r4); empty ranges keep the never-hit box
+    nd.kind = 0;
+    nd.child = (uint32_t)nodes.size();
+    nd.count = 0;
+    nodes.resize(nodes.size() + 4);
+    for (int c = 0; c < 4; c++) memset(&nodes[nd.child + c], 0, sizeof(LbNode));
+    for (int c = 0; c < 4; c++) {
+      if (r[c + 1] <= r[c]) continue;
+      set_box(c, range_box(r[c], r[c + 1]));
+      nd.count++;
+    }
+    nodes[self] = nd;
+    const uint32_t child = nd.child;
+    for (int c = 0; c < 4; c++)
+      if (r[c + 1] > r[c]) build(child + (uint32_t)c, r[c], r[c + 1], levels - 1);
+  }
+};
+
+// Leaf build of order 3.  Returns the leaf's nodes (root first, child links relative to the root)
+// and permutes the records like build_leaf.  Empty result: the leaf stays linear.
+inline std::vector<LbNode> build_leaf_sah(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out,
+                                          float m_floor) {
+  const uint32_t n = job.count, first = job.first;
+  std::vector<Box3> boxes(n);
+  std::vector<float> cen(3 * (size_t)n);
+  for (uint32_t i = 0; i < n; i++) {
+    boxes[i] = record_box(s->tri_plane + 4 * (size_t)(first + i), s->tri_aux[first + i], m_floor);
+    for (int k = 0; k < 3; k++) {
+      float c = 0.5f * (boxes[i].lo[k] + boxes[i].hi[k]);
+      if (!(c == c) || isinf(c)) c = 0.f;
+      cen[3 * (size_t)i + k] = c;
+    }
+  }
+  std::vector<uint32_t> perm(n);
+  for (uint32_t i = 0; i < n; i++) perm[i] = i;
+  std::vector<LbNode> nodes(1);
+  // levels of inner nodes above the quad level: the fewest that hold n, plus two of slack for
+  // uneven cuts, never more than the stack allows
+  int levels = 0;
+  while (SahLeafBuilder::cap(levels) < n) levels++;
+  levels = levels + 2 < FS2_LBVH_MAX_LEVELS - 1 ? levels + 2 : FS2_LBVH_MAX_LEVELS - 1;
+  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}, {}};
+  b.build(0, 0, n, levels);
+  if (nodes.size() >= 65536) return {};  // stack entries carry 16-bit node offsets
+  for (uint32_t i = 0; i < n; i++) {
+    uint32_t src = perm[i];
+    memcpy(&out->plane[4 * (size_t)(first + i)], s->tri_plane + 4 * (size_t)(first + src), 16);
+    out->aux[first + i] = s->tri_aux[first + src];
+    out->order[first + i] = first + src;
+  }
+  return nodes;
+}
+
 }  // namespace lbvh_detail
 
 // Builds the leaf BVHs of every mesh-tree leaf of `s`.  min_leaf: leaves with fewer records
@@ -400,27 +677,58 @@ inline void build_lbvh(const fs_scene_desc* s, LbvhHost* out, uint32_t min_leaf 
       jobs.push_back(j);
     }
   }
-  out->nodes.resize(total_nodes ? total_nodes : 1);
   const float m_floor = out->m_floor = fmaxf(scene_coordinate_scale(s), m_floor_min);
-  for (const LeafJob& j : jobs) out->leaf[j.node].root = j.node_base;
   if (threads == 0) threads = std::thread::hardware_concurrency();
   if (threads == 0) threads = 1;
   if (threads > 32) threads = 32;
-  std::atomic<size_t> next(0);
-  auto work = [&]() {
-    for (;;) {
-      size_t i = next.fetch_add(1);
-      if (i >= jobs.size()) break;
-      build_leaf(s, jobs[i], out, m_floor);
+  auto run = [&](auto&& body) {
+    std::atomic<size_t> next(0);
+    auto work = [&]() {
+      for (;;) {
+        size_t i = next.fetch_add(1);
+        if (i >= jobs.size()) break;
+        body(i);
+      }
+    };
+    if (threads <= 1 || jobs.size() < 8) {
+      work();
+    } else {
+      std::vector<std::thread> pool;
+      for (unsigned t = 0; t < threads; t++) pool.emplace_back(work);
+      for (auto& t : pool) t.join();
     }
   };
-  if (threads <= 1 || jobs.size() < 8) {
-    work();
-  } else {
-    std::vector<std::thread> pool;
-    for (unsigned t = 0; t < threads; t++) pool.emplace_back(work);
-    for (auto& t : pool) t.join();
+#if FS2_LBVH_ORDER == 3
+  // node counts are known only after the build: leaves are built into their own arrays (fat
+  // leaves first, they take longest), then laid out one after the other and their links rebased
+  std::vector<std::vector<LbNode>> built(jobs.size());
+  std::vector<size_t> by_size(jobs.size());
+  for (size_t i = 0; i < jobs.size(); i++) by_size[i] = i;
+  std::sort(by_size.begin(), by_size.end(), [&](size_t a, size_t b) {
+    return jobs[a].count > jobs[b].count || (jobs[a].count == jobs[b].count && a < b);
+  });
+  run([&](size_t i) { built[by_size[i]] = build_leaf_sah(s, jobs[by_size[i]], out, m_floor); });
+  total_nodes = 0;
+  for (size_t i = 0; i < jobs.size(); i++) {
+    jobs[i].node_base = total_nodes;
+    jobs[i].n_nodes = (uint32_t)built[i].size();
+    total_nodes += jobs[i].n_nodes;
   }
+  out->nodes.resize(total_nodes ? total_nodes : 1);
+  run([&](size_t i) {
+    for (uint32_t k = 0; k < jobs[i].n_nodes; k++) {
+      LbNode nd = built[i][k];
+      if (nd.kind == 0) nd.child += jobs[i].node_base;
+      out->nodes[jobs[i].node_base + k] = nd;
+    }
+    if (jobs[i].n_nodes) out->leaf[jobs[i].node].root = jobs[i].node_base;
+    std::vector<LbNode>().swap(built[i]);
+  });
+#else
+  out->nodes.resize(total_nodes ? total_nodes : 1);
+  for (const LeafJob& j : jobs) out->leaf[j.node].root = j.node_base;
+  run([&](size_t i) { build_leaf(s, jobs[i], out, m_floor); });
+#endif
 }
 
 }  // namespace fs2

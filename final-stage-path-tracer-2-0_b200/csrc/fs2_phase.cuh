@@ -50,6 +50,14 @@ static inline unsigned ph_smem_bytes(bool scene_tree) {
 #define FS2_PH_REPEAT_MIN 12   // repeat a phase only while this many lanes are still in it
 #endif
 
+#ifndef FS2_PH_FUSE_DONE
+#define FS2_PH_FUSE_DONE 1  // a walk that ends (root miss, last frame popped) leaves the tree in the same step
+#endif
+
+#ifndef FS2_PH_SKIP_EMPTY
+#define FS2_PH_SKIP_EMPTY 1  // children that are empty leaves are answered from the parent's occupancy byte
+#endif
+
 enum PhState {
   PH_IDLE = 0,
   PH_SEG_START,   // begin Scene::Trace for the lane's ray
@@ -121,6 +129,34 @@ __device__ __forceinline__ LbRay ph_segment_start(const DScene& S, PhLane& w, co
 }
 
 // ------------------------------------------------------------------ octree steps
+// The active tree's walk ended with `ret` (no frame left): Scene::Trace is complete
+// (scene.cpp:234-236) or MeshObject::Trace returns into the object loop (mesh.cpp:277-322).
+template <bool TREE>
+__device__ __forceinline__ void ph_tree_done(const DScene& S, PhLane& w, bool mesh, bool ret) {
+  if (!mesh) {
+    w.st = PH_SHADE;
+    return;
+  }
+  w.flags &= ~PH_F_MESH;
+  if (TREE && S.scene_root >= 0 && ret && w.rec.param < w.glob.param) {
+    w.glob = w.rec;
+    w.flags |= PH_F_SIMPROVED;
+  }
+  w.st = PH_OBJ;
+}
+
+// Node w.cur answered "no hit" before anything was pushed for it: return false to the enclosing
+// frame, or — at the root — end the walk in the same step (a ray that misses a mesh's root box
+// is the common case: one step instead of ENTER + RETURN).
+template <bool TREE>
+__device__ __forceinline__ void ph_enter_miss(const DScene& S, PhLane& w, bool mesh) {
+  w.flags &= ~PH_F_RET;
+  if (FS2_PH_FUSE_DONE && (mesh ? w.msp : w.ssp) == 0)
+    ph_tree_done<TREE>(S, w, mesh, false);
+  else
+    w.st = PH_RETURN;
+}
+
 // "call" node w.cur of the active tree (reference mesh.cpp:78-84 / scene.cpp:76-83, then
 // bvh.h:160-186).  Same arithmetic as walk_octree().
 template <bool STATS, bool TREE = true>
@@ -133,14 +169,12 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
   bool inside;
   if (STATS) c.n_node++;
   if (!ray_box(n.mn, n.mx, r, nparam, entry, inside) || nparam > w.rec.param) {
-    w.flags &= ~PH_F_RET;
-    w.st = PH_RETURN;
+    ph_enter_miss<TREE>(S, w, mesh);
     return;
   }
   if (n.count != FS_NODE_INTERNAL) {
     if (!n.count) {
-      w.flags &= ~PH_F_RET;
-      w.st = PH_RETURN;
+      ph_enter_miss<TREE>(S, w, mesh);
     } else if (!mesh) {
       // scene.cpp:84-99: one leaf-local record, seeded with "no hit"
       w.sleaf_first = n.first;
@@ -186,8 +220,7 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
   int& sp = mesh ? w.msp : w.ssp;
   const int maxd = mesh ? FS2_PH_MESH_FRAMES : FS2_PH_SCENE_FRAMES;
   if (sp >= maxd) {  // deeper than any tree the host builds
-    w.flags &= ~PH_F_RET;
-    w.st = PH_RETURN;
+    ph_enter_miss<TREE>(S, w, mesh);
     return;
   }
   V3 cen = (n.mn + n.mx) * 0.5f;
@@ -202,30 +235,28 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
   sm.f(sm.fslot(mesh, sp, 4)) = nparam;  // st is rebuilt from it (outside origins only)
   sp++;
   w.cur = n.first + (bits & 7u);
+  if (FS2_PH_SKIP_EMPTY && !((n.cmask >> (bits & 7u)) & 1u)) {
+    // the child is an empty leaf: whatever its box test says, it returns "no hit"
+    // (mesh.cpp:78-111 / scene.cpp:76-99 with an empty list) — answered here, without the visit
+    if (STATS) c.n_node++;
+    w.flags &= ~PH_F_RET;
+    w.st = PH_RETURN;
+    return;
+  }
   prefetch_l1(S.nodes + 2 * (size_t)w.cur);
   // stays in PH_ENTER
 }
 
 // Return (w.flags & PH_F_RET) into the enclosing frame of the active tree (bvh.h:189-228),
 // or finish the tree when no frame is left.  One frame per call.
-template <bool TREE = true>
+template <bool STATS, bool TREE = true>
 __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray& r,
-                                          const PhSmem& sm) {
+                                          const PhSmem& sm, Counters& c) {
   const bool mesh = !TREE || (w.flags & PH_F_MESH) != 0;
   int& sp = mesh ? w.msp : w.ssp;
   bool ret = (w.flags & PH_F_RET) != 0;
-  if (sp == 0) {
-    if (!mesh) {  // Scene::Trace finished (scene.cpp:234-236)
-      w.st = PH_SHADE;
-      return;
-    }
-    // MeshObject::Trace finished with `ret` (mesh.cpp:277-322)
-    w.flags &= ~PH_F_MESH;
-    if (TREE && S.scene_root >= 0 && ret && w.rec.param < w.glob.param) {
-      w.glob = w.rec;
-      w.flags |= PH_F_SIMPROVED;
-    }
-    w.st = PH_OBJ;
+  if (sp == 0) {  // (a leaf at the root: the only way here without a frame)
+    ph_tree_done<TREE>(S, w, mesh, ret);
     return;
   }
   const int f = sp - 1;
@@ -237,7 +268,8 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
     bits |= 32u;
     NodeRec ch = load_node(S, pn.first + (bits & 7u));
     if (point_in_box(ch.mn, ch.mx, r.start + r.dir * w.rec.param)) {
-      sp--;  // ret stays true; continue returning into the parent frame
+      // ret stays true; continue returning into the parent frame, or finish with the last one
+      if (--sp == 0 && FS2_PH_FUSE_DONE) ph_tree_done<TREE>(S, w, mesh, true);
       return;
     }
   }
@@ -271,13 +303,19 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
   }
   if (!go) {
     w.flags = (bits & 32u) ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
-    sp--;
+    if (--sp == 0 && FS2_PH_FUSE_DONE) ph_tree_done<TREE>(S, w, mesh, (bits & 32u) != 0u);
     return;  // keep returning
   }
   sm.f(sm.fslot(mesh, f, consumed)) = FS2_INFINITY;
   bits = ((bits ^ flip) & ~(3u << 3)) | (visits << 3);
   sm.w(sm.fslot(mesh, f, 0)) = node | (bits << FS2_PH_NODE_BITS);
   w.cur = pn.first + (bits & 7u);
+  if (FS2_PH_SKIP_EMPTY && !((pn.cmask >> (bits & 7u)) & 1u)) {
+    // empty sibling: it returns "no hit" into this frame; the next step looks for the one after
+    if (STATS) c.n_node++;
+    w.flags &= ~PH_F_RET;
+    return;  // stays in PH_RETURN
+  }
   prefetch_l1(S.nodes + 2 * (size_t)w.cur);
   w.st = PH_ENTER;
 }
@@ -285,27 +323,48 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
 // ------------------------------------------------------------------ object iteration
 // One object of the brute-force list (scene.cpp:230-233) or of the current scene-tree leaf
 // (scene.cpp:84-99).  Primitives are tested on the spot, a mesh starts its octree walk.
+#ifndef FS2_PH_OBJ_BATCH
+#define FS2_PH_OBJ_BATCH 1  // brute-force list: objects looked at per step (until a mesh starts its walk);
+                            // measured on config 2 (fused tree ends, median-split leaf BVH): 1 -> 651, 4 -> 629 Mpaths/s
+#endif
 template <bool STATS, bool TREE = true>
 __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray& r, Counters& c) {
-  uint32_t oi;
   const bool tree = TREE && S.scene_root >= 0;
   if (!tree) {
-    if (w.obj_i >= S.n_objects) {
-      w.st = PH_SHADE;
-      return;
+    // a few list entries per step: primitives are tested on the spot, the end of the list is
+    // noticed in the step that tested the last one
+#pragma unroll 1
+    for (int k = 0; k < FS2_PH_OBJ_BATCH; k++) {
+      if (w.obj_i >= S.n_objects) {
+        w.st = PH_SHADE;
+        return;
+      }
+      const uint32_t oi = w.obj_i++;
+      float4 w0 = obj_word(S, oi, 0);
+      if (__float_as_uint(w0.x) == FS_OBJ_MESH) {
+        uint32_t root = __float_as_uint(w0.z);
+        if (root == 0xFFFFFFFFu) continue;
+        w.cur_obj = oi;
+        w.cur = root;
+        prefetch_l1(S.nodes + 2 * (size_t)root);
+        w.msp = 0;
+        w.flags |= PH_F_MESH;
+        w.st = PH_ENTER;
+        return;
+      }
+      primitive_trace<STATS>(S, oi, __float_as_uint(w0.x), r, w.rec, c);
     }
-    oi = w.obj_i++;
-  } else {
-    if (w.sleaf_i >= w.sleaf_count) {
-      // leaf done: hand the leaf's verdict back to the scene walk
-      w.rec = w.glob;
-      w.flags = (w.flags & PH_F_SIMPROVED) ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
-      w.st = PH_RETURN;
-      return;
-    }
-    oi = __ldg(S.scene_refs + w.sleaf_first + w.sleaf_i);
-    w.sleaf_i++;
+    return;
   }
+  if (w.sleaf_i >= w.sleaf_count) {
+    // leaf done: hand the leaf's verdict back to the scene walk
+    w.rec = w.glob;
+    w.flags = (w.flags & PH_F_SIMPROVED) ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
+    w.st = PH_RETURN;
+    return;
+  }
+  const uint32_t oi = __ldg(S.scene_refs + w.sleaf_first + w.sleaf_i);
+  w.sleaf_i++;
   float4 w0 = obj_word(S, oi, 0);
   if (__float_as_uint(w0.x) == FS_OBJ_MESH) {
     uint32_t root = __float_as_uint(w0.z);
@@ -320,10 +379,126 @@ __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray&
     return;
   }
   bool improved = primitive_trace<STATS>(S, oi, __float_as_uint(w0.x), r, w.rec, c);
-  if (tree && improved && w.rec.param < w.glob.param) {
+  if (improved && w.rec.param < w.glob.param) {
     w.glob = w.rec;
     w.flags |= PH_F_SIMPROVED;
   }
+}
+
+// Warp-cooperative form of the scene-tree leaf loop (scene.cpp:84-99), called by the whole
+// (converged) warp; `owners` = lanes in PH_OBJ.  The reference's tree is shallow — a leaf lists
+// tens of objects — and the per-lane form tests one of them per step at 5-8 active lanes (ncu on
+// the 303-object scene: profiles/r2_*_many303_*).  Here the pending objects of every owner are
+// spread over G = 4 ... 32 lanes (32 / owners, a power of two), one object per lane:
+//   sequential rule: object i replaces the leaf-local record when it is hit at t_i < record.t,
+//   so after a run of primitives the record is the lexicographic minimum (t_i, i) over the hits
+//   below the record the run started with — every lane tests its object against that starting
+//   record and a G-lane min-reduction picks the survivor.  (CuboidObject::Trace's own face loop
+//   has the same form and runs unchanged inside primitive_trace.)
+//   A mesh ends the run: it must see the record left by the objects before it (its octree walk
+//   culls with it), so a group only takes the primitives in front of its first mesh, and an
+//   owner whose next object is a mesh starts that walk itself.
+// slot_owner: 8 bytes of shared memory per warp.
+template <bool STATS>
+__device__ __forceinline__ void ph_object_coop(const DScene& S, PhLane& w, const Ray& r, Counters& c,
+                                               unsigned owners, volatile uint8_t* slot_owner) {
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int lane = threadIdx.x & 31;
+  const unsigned below = (1u << lane) - 1u;
+  const bool own = (owners >> lane) & 1u;
+  if (own && w.sleaf_i >= w.sleaf_count) {
+    // leaf done: hand the leaf's verdict back to the scene walk
+    w.rec = w.glob;
+    w.flags = (w.flags & PH_F_SIMPROVED) ? (w.flags | PH_F_RET) : (w.flags & ~PH_F_RET);
+    w.st = PH_RETURN;
+  }
+  unsigned todo = __ballot_sync(FULL, own && w.st == PH_OBJ);
+  if (!todo) return;
+  // lanes per owner: 32 / owners rounded down to a power of two, at least 4
+  const uint32_t n_own = (uint32_t)__popc(todo);
+  const uint32_t lg = n_own <= 1u ? 5u : n_own <= 2u ? 4u : n_own <= 4u ? 3u : 2u;
+  const uint32_t G = 1u << lg, slots = 32u >> lg;
+  bool start_mesh = false;
+  while (todo) {
+    const uint32_t rank = (uint32_t)__popc(todo & below);
+    const bool served = ((todo >> lane) & 1u) && rank < slots;
+    if (served) slot_owner[rank] = (uint8_t)lane;
+    __syncwarp();
+    const uint32_t n_served = min((uint32_t)__popc(todo), slots);
+    const uint32_t slot = (uint32_t)lane >> lg, j = (uint32_t)lane & (G - 1u);
+    const int src = slot < n_served ? (int)slot_owner[slot] : 0;
+    __syncwarp();
+    const uint32_t base = __shfl_sync(FULL, w.sleaf_first + w.sleaf_i, src);
+    const uint32_t left = __shfl_sync(FULL, w.sleaf_count - w.sleaf_i, src);
+    Ray q;
+    q.start = v3(__shfl_sync(FULL, r.start.x, src), __shfl_sync(FULL, r.start.y, src),
+                 __shfl_sync(FULL, r.start.z, src));
+    q.dir = v3(__shfl_sync(FULL, r.dir.x, src), __shfl_sync(FULL, r.dir.y, src),
+               __shfl_sync(FULL, r.dir.z, src));
+    q.stop = q.start;  // (not read by the primitive tests)
+    q.zero_length = __shfl_sync(FULL, r.zero_length ? 1u : 0u, src) != 0u;
+    const float bt = __shfl_sync(FULL, w.rec.param, src);
+    const bool mine = slot < n_served && j < left;
+    uint32_t oi = 0, type = FS_OBJ_MESH;
+    if (mine) {
+      oi = __ldg(S.scene_refs + base + j);
+      type = __float_as_uint(obj_word(S, oi, 0).x);
+    }
+    // primitives in front of the group's first mesh
+    const unsigned mesh_b = __ballot_sync(FULL, mine && type == FS_OBJ_MESH);
+    const unsigned gmask = G == 32u ? FULL : ((1u << G) - 1u) << (slot << lg);
+    const unsigned gm = mesh_b & gmask;
+    const uint32_t first_mesh = gm ? (uint32_t)__ffs((int)(gm >> (slot << lg))) - 1u : G;
+    Hit h;
+    h.param = FS2_INFINITY;
+    h.object = 0xFFFFFFFFu;
+    h.prim = 0xFFFFFFFFu;
+    h.u = h.v = 0.f;
+    uint32_t key = 0xFFFFFFFFu;  // position in the run: ties keep the first object
+    if (mine && j < first_mesh) {
+      Hit t = h;
+      t.param = bt;
+      if (primitive_trace<STATS>(S, oi, type, q, t, c)) {
+        h = t;
+        key = j;
+      }
+    }
+#pragma unroll
+    for (uint32_t off = 1; off < 32u; off <<= 1) {
+      float ot = __shfl_xor_sync(FULL, h.param, off);
+      uint32_t ok = __shfl_xor_sync(FULL, key, off);
+      uint32_t oo = __shfl_xor_sync(FULL, h.object, off), op = __shfl_xor_sync(FULL, h.prim, off);
+      if (off < G && (ot < h.param || (ot == h.param && ok < key))) {
+        h.param = ot;
+        key = ok;
+        h.object = oo;
+        h.prim = op;
+      }
+    }
+    // hand the slot's verdict back to its owner
+    const int from = served ? (int)(rank << lg) : 0;
+    const float rt = __shfl_sync(FULL, h.param, from);
+    const uint32_t rk = __shfl_sync(FULL, key, from);
+    const uint32_t ro = __shfl_sync(FULL, h.object, from), rp = __shfl_sync(FULL, h.prim, from);
+    const uint32_t rfm = __shfl_sync(FULL, first_mesh, from);
+    if (served) {
+      const uint32_t avail = min(w.sleaf_count - w.sleaf_i, G);
+      const uint32_t take = min(avail, rfm);
+      w.sleaf_i += take;
+      if (rk != 0xFFFFFFFFu) {
+        w.rec.param = rt;
+        w.rec.object = ro;
+        w.rec.prim = rp;
+        if (w.rec.param < w.glob.param) {
+          w.glob = w.rec;
+          w.flags |= PH_F_SIMPROVED;
+        }
+      }
+      if (take == 0u) start_mesh = true;  // the next object is a mesh
+    }
+    todo &= ~__ballot_sync(FULL, served);
+  }
+  if (start_mesh) ph_object<STATS, true>(S, w, r, c);
 }
 
 // ------------------------------------------------------------------ leaf BVH steps

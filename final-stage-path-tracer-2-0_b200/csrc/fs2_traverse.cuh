@@ -249,15 +249,22 @@ struct Frame {
 struct NodeRec {
   V3 mn, mx;
   uint32_t first, count;
+  uint32_t cmask;  // internal nodes: bit c set = child c is not an empty leaf
 };
 
+// Device copy of fs_node (tag_nodes() in fs2_cabi.cu): the `first` word of an internal node
+// carries the occupancy of its eight children in its top byte (node indices are < 2^24).
+#define FS2_NODE_INDEX_BITS 24
 __device__ __forceinline__ NodeRec load_node(const DScene& S, uint32_t i) {
   float4 a = __ldg(S.nodes + 2 * (size_t)i), b = __ldg(S.nodes + 2 * (size_t)i + 1);
   NodeRec n;
   n.mn = v3(a.x, a.y, a.z);
-  n.first = __float_as_uint(a.w);
   n.mx = v3(b.x, b.y, b.z);
   n.count = __float_as_uint(b.w);
+  const uint32_t f = __float_as_uint(a.w);
+  const bool internal = n.count == FS_NODE_INTERNAL;
+  n.first = internal ? (f & ((1u << FS2_NODE_INDEX_BITS) - 1u)) : f;
+  n.cmask = internal ? (f >> FS2_NODE_INDEX_BITS) : 0u;
   return n;
 }
 

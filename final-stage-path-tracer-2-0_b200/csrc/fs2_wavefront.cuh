@@ -198,6 +198,12 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #ifndef FS2_WF_REP_RETURN
 #define FS2_WF_REP_RETURN 4
 #endif
+#ifndef FS2_WF_COOP_OBJ
+#define FS2_WF_COOP_OBJ 1  // scene-tree leaves: objects tested by 4 ... 32 lanes per owner (ph_object_coop)
+#endif
+#ifndef FS2_WF_REPEAT_MIN_OBJ
+#define FS2_WF_REPEAT_MIN_OBJ 2
+#endif
 #ifndef FS2_WF_COOP_TRIS
 #define FS2_WF_COOP_TRIS 1  // triangle groups tested by 4 lanes each (ph_lb_tris_coop)
 #endif
@@ -207,7 +213,9 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 // TREE = false: the scene has no scene octree (< 182 objects), which lets the
 // compiler drop the scene-leaf bookkeeping (second hit record, leaf cursor) from the loop.
 template <bool STATS, bool TREE>
-__global__ void __launch_bounds__(FS2_PH_THREADS, FS2_WF_MIN_BLOCKS)
+// (with a scene tree the per-lane stacks are 252 B: shared memory holds 7 CTAs per SM, so that
+// specialisation may use the registers of 7)
+__global__ void __launch_bounds__(FS2_PH_THREADS, TREE ? (FS2_WF_MIN_BLOCKS < 7 ? FS2_WF_MIN_BLOCKS : 7) : FS2_WF_MIN_BLOCKS)
 k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict__ stats) {
   extern __shared__ uint32_t ph_smem[];
   __shared__ uint8_t s_slot_owner[FS2_PH_THREADS / 32][8];
@@ -274,8 +282,17 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
       }
     }
     // scene-tree leaves hold tens of objects (the reference's tree is shallow): stay in the phase
-    FS2_PHASE_N(PH_OBJ, (TREE ? FS2_WF_REP_OBJ_TREE : FS2_WF_REP_OBJ), FS2_WF_REPEAT_MIN,
-                (ph_object<STATS, TREE>(S, w, ray, c)))
+    if (TREE && FS2_WF_COOP_OBJ && S.scene_root >= 0) {
+#pragma unroll 1
+      for (int rep_ = 0; rep_ < FS2_WF_REP_OBJ_TREE; ++rep_) {
+        unsigned m_ = __ballot_sync(FULL, w.st == PH_OBJ);
+        if (!m_ || (rep_ && __popc(m_) < FS2_WF_REPEAT_MIN_OBJ)) break;
+        ph_object_coop<STATS>(S, w, ray, c, m_, s_slot_owner[threadIdx.x >> 5]);
+      }
+    } else {
+      FS2_PHASE_N(PH_OBJ, (TREE ? FS2_WF_REP_OBJ_TREE : FS2_WF_REP_OBJ), FS2_WF_REPEAT_MIN,
+                  (ph_object<STATS, TREE>(S, w, ray, c)))
+    }
     FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, (ph_enter<STATS, TREE>(S, w, ray, sm, c)))
     FS2_PHASE_N(PH_LB_NODE, FS2_WF_REP_NODE, FS2_WF_REPEAT_MIN, ph_lb_node<STATS>(S, w, ray, q, sm, c))
 #if FS2_WF_COOP_TRIS
@@ -288,7 +305,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
 #else
     FS2_PHASE_N(PH_LB_TRIS, FS2_WF_REP_TRIS, FS2_WF_REPEAT_MIN, ph_lb_tris<STATS>(S, w, ray, sm, c))
 #endif
-    FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, ph_return<TREE>(S, w, ray, sm))
+    FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, (ph_return<STATS, TREE>(S, w, ray, sm, c)))
     if (w.st == PH_SHADE) {  // nearest hit of the segment is final
       wf_store_hit(B, idx, w.rec);
       w.st = PH_IDLE;

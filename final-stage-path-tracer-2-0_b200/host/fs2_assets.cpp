@@ -214,6 +214,13 @@ bool load_hdr(const std::string& path, Image* out) {
   const char* nl = strchr(res, '\n');
   if (!nl) return false;
   p = (const unsigned char*)nl + 1;
+  // the header is untrusted: every scanline takes at least 4 bytes of file (an RLE line starts
+  // with a 4-byte marker, a flat one is 4*w), so a size the file cannot hold is refused before
+  // anything is allocated
+  const size_t left = (size_t)(end - p);
+  if ((size_t)h > left / 4 || (size_t)w > (size_t)1 << 20 || (size_t)w * (size_t)h > (size_t)1 << 28)
+    return false;
+  if ((w < 8 || w >= 32768) && (size_t)w * 4 * (size_t)h > left) return false;  // flat lines only
   std::vector<unsigned char> scan((size_t)w * 4);
   out->width = (uint32_t)w;
   out->height = (uint32_t)h;

@@ -2,11 +2,14 @@
 // surface used from Python.  This is where the reference's seam (source/engine.h:68-75)
 // meets the C ABI: flatten-if-dirty -> fs_scene_upload -> fs_trace / fs_first_hit ->
 // fs_film_read into the DisplayFrame's host buffers.  No tracing happens on the host.
+#include <stddef.h>
 #include <stdio.h>
 #include <string.h>
 
 #include <algorithm>
+#include <exception>
 #include <memory>
+#include <string>
 #include <vector>
 
 #include "fs2_impl.h"
@@ -26,8 +29,41 @@ struct TraceState {
   uint64_t scene_version = 0;
   const void* frame = nullptr;  // FrameImpl that owns the device film
   uint32_t film_w = 0, film_h = 0;
+  // identity of what the device film accumulates (checkpoint header): the last scene / camera
+  // traced into it, and — after LoadFilmCheckpoint — what the next TraceSamples must match
+  uint64_t scene_hash = 0, camera_hash = 0;
+  bool expect_identity = false;
+  uint64_t expect_seed = 0, expect_scene = 0, expect_camera = 0;
   char error[512] = "";
 };
+
+// FNV-1a over a byte range (identity check, not a security boundary)
+uint64_t fnv(const void* p, size_t n, uint64_t h = 0xcbf29ce484222325ull) {
+  const unsigned char* b = (const unsigned char*)p;
+  for (size_t i = 0; i < n; i++) h = (h ^ b[i]) * 0x100000001b3ull;
+  return h;
+}
+// Small arrays in full, the big ones by their size and both ends (a render is not resumed on
+// "almost the same" mesh by accident; hashing a gigabyte on every upload is not worth more).
+uint64_t hash_range(const void* p, size_t bytes, uint64_t h) {
+  const size_t edge = 1 << 16;
+  h = fnv(&bytes, sizeof bytes, h);
+  if (!p || !bytes) return h;
+  if (bytes <= 2 * edge) return fnv(p, bytes, h);
+  h = fnv(p, edge, h);
+  return fnv((const char*)p + bytes - edge, edge, h);
+}
+uint64_t hash_scene(const fs_scene_desc* d) {
+  uint64_t h = fnv(d, offsetof(fs_scene_desc, nodes));
+  h = hash_range(d->nodes, (size_t)d->n_nodes * sizeof(fs_node), h);
+  h = hash_range(d->scene_refs, (size_t)d->n_scene_refs * 4, h);
+  h = hash_range(d->tri_plane, (size_t)d->n_tris * 16, h);
+  h = hash_range(d->faces, (size_t)d->n_faces * sizeof(fs_face_attr), h);
+  h = hash_range(d->objects, (size_t)d->n_objects * sizeof(fs_object), h);
+  h = hash_range(d->materials, (size_t)d->n_materials * sizeof(fs_material), h);
+  h = hash_range(d->textures, (size_t)d->n_textures * sizeof(fs_texture), h);
+  return hash_range(d->texels, (size_t)d->n_texels * 4, h);
+}
 
 TraceState& state() {
   static TraceState s;
@@ -76,6 +112,7 @@ int ensure_scene(base::Scene* scene) {
   if (fs_scene_upload(st.ctx, d) != FS_OK) return fail("fs_scene_upload", st.ctx);
   st.scene = si;
   st.scene_version = si->flat_version;
+  st.scene_hash = hash_scene(d);
   return 0;
 }
 
@@ -148,6 +185,7 @@ void DisplayFrame::Reset() {  // frame.cpp:43-51
   std::fill(f.mat_id.begin(), f.mat_id.end(), (uint64_t)0);
   f.samples = 0;
   f.device_dirty = true;
+  if (state().frame == impl_.get()) state().expect_identity = false;
 }
 uint8* DisplayFrame::GetDisplayBuffer() { return impl_->rgb8.data(); }
 uint32 DisplayFrame::GetWidth() { return impl_->width; }
@@ -203,6 +241,18 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
     f->samples = 0;
   }
   fs_camera cam = to_pod(view);
+  st.camera_hash = fnv(&cam, sizeof cam);
+  if (st.expect_identity) {
+    // a resumed film continues one image: same scene, same camera, same seed (the sample
+    // sequence restarts at the stored count, so another seed would merely be unreproducible,
+    // but another scene or camera blends two pictures)
+    if (st.expect_scene != st.scene_hash || st.expect_camera != st.camera_hash || st.expect_seed != st.seed) {
+      fail_msg("TraceSamples: the resumed checkpoint was written for another scene, camera or seed "
+               "(Reset() the frame to start a new image)");
+      return -1;
+    }
+    st.expect_identity = false;
+  }
   if (fs_trace(st.ctx, &cam, f->samples, n_samples, 1, st.seed, FS_TRACE_DEFAULT | st.shard_flags) != FS_OK)
     return fail("fs_trace", st.ctx);
   f->samples += n_samples;
@@ -215,8 +265,9 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
 
 namespace {
 struct CheckpointHeader {
-  char magic[8];  // "FS2FILM1"
+  char magic[8];  // "FS2FILM2"
   uint32_t width, height, samples, reserved;
+  uint64_t seed, scene_hash, camera_hash;  // what the sums were accumulated from
 };
 }  // namespace
 
@@ -255,7 +306,8 @@ bool SaveFilmCheckpoint(DisplayFrame* frame, const char* path) {
   }
   FILE* fp = fopen(path, "wb");
   if (!fp) return false;
-  CheckpointHeader h = {{'F', 'S', '2', 'F', 'I', 'L', 'M', '1'}, f->width, f->height, f->samples, 0};
+  CheckpointHeader h = {{'F', 'S', '2', 'F', 'I', 'L', 'M', '2'}, f->width, f->height, f->samples, 0,
+                        st.seed, st.scene_hash, st.camera_hash};
   bool ok = fwrite(&h, sizeof h, 1, fp) == 1 && fwrite(sums.data(), 4, sums.size(), fp) == sums.size();
   return fclose(fp) == 0 && ok;
 }
@@ -268,7 +320,7 @@ bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path) {
   if (!fp) return false;
   CheckpointHeader h;
   std::vector<float> sums((size_t)f->width * f->height * 4);
-  bool ok = fread(&h, sizeof h, 1, fp) == 1 && !memcmp(h.magic, "FS2FILM1", 8) &&
+  bool ok = fread(&h, sizeof h, 1, fp) == 1 && !memcmp(h.magic, "FS2FILM2", 8) &&
             h.width == f->width && h.height == f->height &&
             fread(sums.data(), 4, sums.size(), fp) == sums.size();
   fclose(fp);
@@ -294,6 +346,10 @@ bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path) {
   f->device_dirty = false;
   f->samples = h.samples;
   f->frame_count = h.samples;
+  st.expect_identity = h.samples > 0;
+  st.expect_seed = h.seed;
+  st.expect_scene = h.scene_hash;
+  st.expect_camera = h.camera_hash;
   return true;
 }
 
@@ -322,7 +378,16 @@ extern "C" {
 
 void* fs2h_scene_new() { return new base::Scene(); }
 void fs2h_scene_free(void* s) { delete (base::Scene*)s; }
-int fs2h_scene_load(void* s, const char* path) { return ((base::Scene*)s)->LoadScene(path) ? 0 : -1; }
+// Nothing may unwind through the C surface: a damaged asset that drives an allocation over the
+// edge (std::bad_alloc / length_error) is a load failure, not an abort.
+int fs2h_scene_load(void* s, const char* path) {
+  try {
+    return ((base::Scene*)s)->LoadScene(path) ? 0 : -1;
+  } catch (const std::exception& e) {
+    fail_msg((std::string("fs2h_scene_load: ") + e.what()).c_str());
+    return -1;
+  }
+}
 void fs2h_initialize_materials() { base::InitializeMaterials(); }
 // Restarts the process-wide random stream at the reference's default state, so that a
 // scene loaded later in the same process gets the ids / normal table a fresh process would.
@@ -390,9 +455,14 @@ int fs2h_load_image(const char* path, uint32_t* width, uint32_t* height, float* 
   fs2h::Image img;
   std::string p = path ? path : "", err;
   auto ends = [&](const char* e) { return p.size() >= strlen(e) && p.compare(p.size() - strlen(e), strlen(e), e) == 0; };
-  bool ok = ends(".bmp") ? fs2h::load_bmp(p, &img)
-          : ends(".hdr") ? fs2h::load_hdr(p, &img)
-          : ends(".exr") ? fs2h::load_exr(p, &img, &err) : false;
+  bool ok = false;
+  try {
+    ok = ends(".bmp") ? fs2h::load_bmp(p, &img)
+       : ends(".hdr") ? fs2h::load_hdr(p, &img)
+       : ends(".exr") ? fs2h::load_exr(p, &img, &err) : false;
+  } catch (const std::exception& e) {
+    err = e.what();
+  }
   if (!ok) {
     fail_msg(("fs2h_load_image: " + p + ": " + (err.empty() ? "unreadable" : err)).c_str());
     return -1;

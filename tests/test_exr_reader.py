@@ -1,8 +1,9 @@
 """the .exr texture reader of the host side (host/fs2_exr.cpp) against
 files written by scenes/exr_write.py from the published OpenEXR layout.  The reference reads .exr
-through tinyexr's LoadEXR (source/material.cpp:70-92), a third-party header that is not in
-/root/reference, so the format specification is the anchor: values must come back exactly
-(HALF -> float conversion is exact), rows top to bottom, R / G / B picked by name."""
+through tinyexr's LoadEXR (source/material.cpp:70-92, source/third_party/tiny_exr_loader.h);
+tests/test_exr_reference.py pins the reader against the texel arrays that loader produced
+(tests/golden/exr_textures.npz).  This file covers the format itself: values must come back
+exactly (HALF -> float conversion is exact), rows top to bottom, R / G / B picked by name."""
 import ctypes as C
 import os
 
@@ -198,3 +199,21 @@ def test_readers_refuse_a_directory(tmp_path):
                      "sphere\n{\n material m\n position 0 0 0\n radius 1\n}\n" % tmp_path)
     hs = host.HostScene(str(scene))  # the mesh fails to load, the scene still does
     assert hs.desc().n_objects >= 1
+
+
+def test_hdr_header_cannot_size_an_allocation(tmp_path):
+    """A 40-byte .hdr that claims 100 000 x 100 000 texels is refused before anything is
+    allocated (it used to reach vector::assign and unwind through the C surface), and a real
+    small file still loads."""
+    big = tmp_path / "huge.hdr"
+    big.write_bytes(b"#?RADIANCE\nFORMAT=32-bit_rle_rgbe\n\n-Y 100000 +X 100000\n" + b"\x00" * 8)
+    rc, _ = _load(str(big))
+    assert rc == -1
+    tall = tmp_path / "tall.hdr"  # plausible width, more lines than the file has bytes for
+    tall.write_bytes(b"#?RADIANCE\n\n-Y 5000 +X 16\n" + b"\x80" * 64)
+    rc, _ = _load(str(tall))
+    assert rc == -1
+    ok = tmp_path / "ok.hdr"
+    ok.write_bytes(b"#?RADIANCE\n\n-Y 2 +X 3\n" + bytes([128, 64, 32, 129] * 6))
+    rc, img = _load(str(ok))
+    assert rc == 0 and img.shape == (2, 3, 3) and np.allclose(img[0, 0], [1.0, 0.5, 0.25])

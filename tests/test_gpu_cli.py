@@ -57,6 +57,14 @@ def test_cli_checkpoint_resume_continues_the_sample_sequence(tmp_path):
     assert np.allclose(whole, resumed, rtol=1e-5, atol=1e-6)
     bad = subprocess.run(common + ["-w", "64", "--spp", "1", "--resume", ck], capture_output=True, text=True)
     assert bad.returncode != 0  # a checkpoint of another frame size is refused
+    # ... and so is one of another image: the header carries the seed and hashes of the flattened
+    # scene and of the camera the sums were accumulated from
+    other = gen_scenes.generate(str(tmp_path), ["demo_dof"])["demo_dof"]
+    for argv in ([exe, "-f", other, "-w", "80", "-h", "48", "--seed", "9"],
+                 [exe, "-f", scene, "-w", "80", "-h", "48", "--seed", "10"]):
+        bad = subprocess.run(argv + ["--spp", "1", "--resume", ck, "--out", str(tmp_path / "bad.ppm")],
+                             capture_output=True, text=True)
+        assert bad.returncode != 0 and "another scene, camera or seed" in bad.stderr, bad.stderr
 
 
 def test_cli_post_processing_output(tmp_path):
