@@ -63,6 +63,11 @@ class fs_scene_desc(C.Structure):
                 ("lut", C.c_void_p)]
 
 
+# fs_ray_hit (fs_trace_rays)
+RAY_HIT_DT = np.dtype([("param", "<f4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("uv", "<f4", 2),
+                       ("object", "<u4"), ("face", "<u4"), ("material", "<u4"), ("is_internal", "<u4")])
+
+
 class fs_camera(C.Structure):
     _fields_ = [("origin", C.c_float * 3), ("target", C.c_float * 3), ("fov_y", C.c_float),
                 ("aperture_size", C.c_float), ("focal_depth", C.c_float), ("z_near", C.c_float),

@@ -39,7 +39,7 @@ struct DeviceBuf {
 }  // namespace
 
 #define FS2_WF_AHEAD 4  // waves kept enqueued per pipe
-#define FS2_WF_PIPES 2  // independent halves of the path pool (two streams)
+#define FS2_WF_PIPES 8  // most independent parts of the path pool (one stream each); ctx->pipes are used
 
 struct fs_ctx {
   int device = 0;
@@ -61,14 +61,17 @@ struct fs_ctx {
   DeviceBuf wf_planes, wf_hit, wf_counters;  // wavefront path state
   uint32_t* wf_host_live = nullptr;   // pinned: live paths of the newest wave, per pipe
   cudaEvent_t wf_events[FS2_WF_AHEAD * FS2_WF_PIPES] = {};
-  cudaStream_t wf_stream = nullptr;   // second pipe
-  cudaEvent_t wf_fork = nullptr, wf_join = nullptr;
+  cudaStream_t wf_streams[FS2_WF_PIPES] = {};  // [0] unused (the context's stream), [p] pipe p
+  cudaStream_t wf_stream = nullptr;            // == wf_streams[1]: "the pipeline has been set up"
+  cudaEvent_t wf_fork = nullptr, wf_join[FS2_WF_PIPES] = {};
+  int pipes = 2;  // FS2_PIPES: parts the pool is split into
   int sm_count = 148;
   // stats
   unsigned long long* d_stats = nullptr;
   uint64_t launches = 0;
   float last_trace_ms = 0.f, last_kernel_ms = 0.f;
   bool stats_build = false;
+  const char* timeline = nullptr;  // FS2_TIMELINE=file: per-launch device time stamps of the wavefront pipeline
   uint32_t tune = 8;  // FS2_TUNE: bits 0-4 idle lanes that trigger a refill in k_wf_trace, bits 8.. pool size (1024 paths)
   // interleaved tile sharding of this context (fs_set_tile_shard); tile_n <= 1: every tile
   uint32_t tile_n = 1, tile_r = 0;
@@ -332,7 +335,7 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
       if (pool > fit) pool = fit;
     }
   }
-  int pipes = (ctx->tune & 32u) || pool < (1u << 18) ? 1 : FS2_WF_PIPES;  // FS2_TUNE bit 5: one pipe
+  int pipes = (ctx->tune & 32u) || pool < (1u << 18) ? 1 : ctx->pipes;  // FS2_TUNE bit 5: one pipe
   const uint32_t cap = (uint32_t)(((pool + pipes - 1) / pipes + 127u) & ~127ull);
   int rc;
   if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * pipes * FS2_WF_PLANES * 16 * 2))) return rc;
@@ -342,9 +345,12 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
     CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->wf_host_live, 64, cudaHostAllocMapped));
     for (int i = 0; i < FS2_WF_AHEAD * FS2_WF_PIPES; i++)
       CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_events[i], cudaEventDisableTiming));
-    CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->wf_stream, cudaStreamNonBlocking));
+    for (int p = 1; p < FS2_WF_PIPES; p++) {
+      CUDA_TRY(ctx, cudaStreamCreateWithFlags(&ctx->wf_streams[p], cudaStreamNonBlocking));
+      CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_join[p], cudaEventDisableTiming));
+    }
+    ctx->wf_stream = ctx->wf_streams[1];
     CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_fork, cudaEventDisableTiming));
-    CUDA_TRY(ctx, cudaEventCreateWithFlags(&ctx->wf_join, cudaEventDisableTiming));
   }
   WfBuffers B[FS2_WF_PIPES];
   cudaStream_t streams[FS2_WF_PIPES];
@@ -362,16 +368,41 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
     B[p].total = total;
     B[p].tile_n = tile_n;
     B[p].tile_r = ctx->tile_r;
-    streams[p] = p == 0 ? ctx->stream : ctx->wf_stream;
+    streams[p] = p == 0 ? ctx->stream : ctx->wf_streams[p];
     *(volatile uint32_t*)(ctx->wf_host_live + p) = 1u;
   }
   CUDA_TRY(ctx, cudaMemsetAsync(ctx->wf_counters.p, 0, 64 * (FS2_WF_PIPES + 1), ctx->stream));
   if (pipes > 1) {
     CUDA_TRY(ctx, cudaEventRecord(ctx->wf_fork, ctx->stream));
-    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->wf_stream, ctx->wf_fork, 0));
+    for (int p = 1; p < pipes; p++) CUDA_TRY(ctx, cudaStreamWaitEvent(streams[p], ctx->wf_fork, 0));
   }
-  for (int p = 0; p < pipes; p++)
+  // FS2_TIMELINE (diagnostics only): a timing event after every launch; written out as
+  // "pipe wave kernel end_ms live" rows relative to the start of the fill when the frame is done
+  struct Stamp {
+    int pipe;
+    unsigned long long wave;
+    const char* what;
+    uint32_t live;
+    cudaEvent_t ev;
+  };
+  std::vector<Stamp> stamps;
+  cudaEvent_t tl_start = nullptr;
+  auto stamp = [&](int p, unsigned long long wave, const char* what, uint32_t live) {
+    if (!ctx->timeline) return;
+    Stamp s{p, wave, what, live, nullptr};
+    cudaEventCreate(&s.ev);
+    cudaEventRecord(s.ev, streams[p]);
+    stamps.push_back(s);
+  };
+  if (ctx->timeline) {
+    cudaEventCreate(&tl_start);
+    cudaEventRecord(tl_start, ctx->stream);
+    for (int p = 1; p < pipes; p++) cudaStreamWaitEvent(streams[p], tl_start, 0);
+  }
+  for (int p = 0; p < pipes; p++) {
     k_wf_shade<true><<<cap / 128u, 128, 0, streams[p]>>>(ctx->ds, cb, film, tp, B[p], ctx->d_stats);
+    stamp(p, 0, "fill", cap);
+  }
   ctx->launches += pipes;
   // every path has at most 8 segments and the pool is refilled every wave
   const unsigned long long max_waves = 8ull * ((total + pool - 1) / pool) + 8ull;
@@ -398,6 +429,7 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
       if (wave >= FS2_WF_AHEAD) {
         CUDA_TRY(ctx, cudaEventSynchronize(ev));
         const uint32_t live = *(volatile uint32_t*)(ctx->wf_host_live + p);
+        if (ctx->timeline) stamps.push_back(Stamp{p, wave - FS2_WF_AHEAD, "live", live, nullptr});
         if (live == 0u) {
           done[p] = true;
           continue;
@@ -408,15 +440,34 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
       running++;
       k_wf_flip<<<1, 1, 0, streams[p]>>>(B[p].counters, B[p].host_live);
       CUDA_TRY(ctx, cudaEventRecord(ev, streams[p]));
+      stamp(p, wave, "flip", live_bound[p]);
       trace_kernel<<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
+      stamp(p, wave, "trace", live_bound[p]);
       k_wf_shade<false><<<shade_blocks, 128, 0, streams[p]>>>(ctx->ds, cb, film, tp, B[p], ctx->d_stats);
+      stamp(p, wave, "shade", live_bound[p]);
       ctx->launches += 3;
     }
     if (!running) break;
   }
-  if (pipes > 1) {
-    CUDA_TRY(ctx, cudaEventRecord(ctx->wf_join, ctx->wf_stream));
-    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->wf_join, 0));
+  for (int p = 1; p < pipes; p++) {
+    CUDA_TRY(ctx, cudaEventRecord(ctx->wf_join[p], streams[p]));
+    CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->wf_join[p], 0));
+  }
+  if (ctx->timeline) {
+    cudaStreamSynchronize(ctx->stream);
+    if (FILE* f = fopen(ctx->timeline, "a")) {
+      fprintf(f, "# frame %dx%d, %u samples, pool %llu in %d pipe(s)\n", film.width, film.height,
+              tp.n_samples, (unsigned long long)cap * pipes, pipes);
+      for (const Stamp& s : stamps) {
+        float ms = 0.f;
+        if (s.ev) cudaEventElapsedTime(&ms, tl_start, s.ev);
+        fprintf(f, "%d %llu %s %.4f %u\n", s.pipe, s.wave, s.what, ms, s.live);
+      }
+      fclose(f);
+    }
+    for (const Stamp& s : stamps)
+      if (s.ev) cudaEventDestroy(s.ev);
+    cudaEventDestroy(tl_start);
   }
   CUDA_TRY(ctx, cudaGetLastError());
   return FS_OK;
@@ -427,7 +478,8 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
 int launch_wavefront(fs_ctx* ctx, const CamBasis& cb, const Film& film, const TraceParams& tp) {
   int rc = launch_wavefront_waves(ctx, cb, film, tp);
   if (rc) {
-    if (ctx->wf_stream) cudaStreamSynchronize(ctx->wf_stream);
+    for (int p = 1; p < FS2_WF_PIPES; p++)
+      if (ctx->wf_streams[p]) cudaStreamSynchronize(ctx->wf_streams[p]);
     cudaStreamSynchronize(ctx->stream);
     cudaGetLastError();
   }
@@ -555,7 +607,8 @@ int ensure_lbvh_for_camera(fs_ctx* ctx, const fs_camera* cam) {
   d.tri_plane = plane.data();
   d.tri_aux = aux.data();
   d.objects = objects.data();
-  if (ctx->wf_stream) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->wf_stream));
+  for (int p = 1; p < FS2_WF_PIPES; p++)
+    if (ctx->wf_streams[p]) CUDA_TRY(ctx, cudaStreamSynchronize(ctx->wf_streams[p]));
   LbvhHost lb;
   build_lbvh(&d, &lb, 9, 0, m / 2.0f);  // limit = 3 * m_floor >= 1.5 * |camera|
   return upload_lbvh(ctx, lb);
@@ -585,6 +638,11 @@ int fs_create(fs_ctx** out, int device, int flags) {
   ctx->device = device;
   ctx->stats_build = (flags & 1) != 0;
   if (const char* e = getenv("FS2_TUNE")) ctx->tune = (uint32_t)strtoul(e, nullptr, 0);
+  ctx->timeline = getenv("FS2_TIMELINE");
+  if (const char* e = getenv("FS2_PIPES")) {
+    int n = atoi(e);
+    ctx->pipes = n < 1 ? 1 : n > FS2_WF_PIPES ? FS2_WF_PIPES : n;
+  }
   int rc = set_device(ctx);
   if (rc == FS_OK) {
     cudaError_t e1 = cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking);
@@ -697,9 +755,11 @@ int fs_destroy(fs_ctx* ctx) {
   if (ctx->wf_host_live) {
     cudaFreeHost(ctx->wf_host_live);
     for (cudaEvent_t e : ctx->wf_events) cudaEventDestroy(e);
-    if (ctx->wf_stream) cudaStreamDestroy(ctx->wf_stream);
+    for (int p = 1; p < FS2_WF_PIPES; p++) {
+      if (ctx->wf_streams[p]) cudaStreamDestroy(ctx->wf_streams[p]);
+      if (ctx->wf_join[p]) cudaEventDestroy(ctx->wf_join[p]);
+    }
     if (ctx->wf_fork) cudaEventDestroy(ctx->wf_fork);
-    if (ctx->wf_join) cudaEventDestroy(ctx->wf_join);
   }
   if (ctx->ev0) cudaEventDestroy(ctx->ev0);
   if (ctx->ev1) cudaEventDestroy(ctx->ev1);
@@ -839,6 +899,48 @@ int fs_trace_range(fs_ctx* ctx, const fs_camera* cam, int width, int height, flo
   ctx->launches++;
   CUDA_TRY(ctx, cudaGetLastError());
   CUDA_TRY(ctx, cudaMemcpyAsync(range, d_range, 4, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_trace_rays(fs_ctx* ctx, const float* segments, int n_rays, fs_ray_hit* out) {
+  if (!ctx || n_rays < 0 || (n_rays && (!segments || !out)))
+    return fail(ctx, FS_E_INVALID, "fs_trace_rays: bad argument");
+  if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_trace_rays before fs_scene_upload");
+  if (!n_rays) return FS_OK;
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  // origins beyond the leaf BVHs' pad range take the linear leaf scans on the device
+  // (DScene::lb_origin_limit), so no rebuild is needed here
+  const size_t in_b = (size_t)n_rays * 24, out_b = (size_t)n_rays * sizeof(fs_ray_hit);
+  if ((rc = dev_alloc(ctx, &ctx->scratch, in_b + out_b + 64))) return rc;
+  float* d_seg = (float*)ctx->scratch.p;
+  fs_ray_hit* d_out = (fs_ray_hit*)((char*)ctx->scratch.p + ((in_b + 63) & ~(size_t)63));
+  CUDA_TRY(ctx, cudaMemcpyAsync(d_seg, segments, in_b, cudaMemcpyHostToDevice, ctx->stream));
+  k_probe_rays<<<(n_rays + FS2_LB_THREADS - 1) / FS2_LB_THREADS, FS2_LB_THREADS, 0, ctx->stream>>>(
+      ctx->ds, d_seg, n_rays, d_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaMemcpyAsync(out, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+int fs_sample_sky(fs_ctx* ctx, const float* views, int n, float* rgb) {
+  if (!ctx || n < 0 || (n && (!views || !rgb))) return fail(ctx, FS_E_INVALID, "fs_sample_sky: bad argument");
+  if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_sample_sky before fs_scene_upload");
+  if (!n) return FS_OK;
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  const size_t b = (size_t)n * 12;
+  if ((rc = dev_alloc(ctx, &ctx->scratch, 2 * b + 64))) return rc;
+  float* d_in = (float*)ctx->scratch.p;
+  float* d_out = (float*)((char*)ctx->scratch.p + ((b + 63) & ~(size_t)63));
+  CUDA_TRY(ctx, cudaMemcpyAsync(d_in, views, b, cudaMemcpyHostToDevice, ctx->stream));
+  k_probe_sky<<<(n + 127) / 128, 128, 0, ctx->stream>>>(ctx->ds, d_in, n, d_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaMemcpyAsync(rgb, d_out, b, cudaMemcpyDeviceToHost, ctx->stream));
   CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
   return FS_OK;
 }

@@ -83,6 +83,54 @@ k_first_hit(DScene S, CamBasis cam, int width, int height, float* __restrict__ o
   warp_add(stats + ST_TRITEST, c.n_tritest);
 }
 
+// Scene::Trace for a list of caller-supplied segments (fs_trace_rays): one thread per ray.
+__global__ void __launch_bounds__(FS2_LB_THREADS)
+k_probe_rays(DScene S, const float* __restrict__ seg, int n, fs_ray_hit* __restrict__ out) {
+  __shared__ uint2 lb_stack[FS2_LB_STACK * FS2_LB_THREADS];
+  const int i = blockIdx.x * FS2_LB_THREADS + threadIdx.x;
+  if (i >= n) return;
+  Counters c = {0, 0, 0, 0, 0, 0};
+  const float* g = seg + 6 * (size_t)i;
+  Ray r = make_ray(v3(g[0], g[1], g[2]), v3(g[3], g[4], g[5]));
+  Hit h = scene_trace<false, true>(S, r, c, lb_stack + threadIdx.x);
+  fs_ray_hit o;
+  o.param = FS_NO_HIT_PARAM;
+  o.point[0] = o.point[1] = o.point[2] = 0.f;
+  o.normal[0] = o.normal[1] = o.normal[2] = 0.f;
+  o.uv[0] = o.uv[1] = 0.f;
+  o.object = 0xFFFFFFFFu;
+  o.face = 0xFFFFFFFFu;
+  o.material = S.sky_material;
+  o.is_internal = 0;
+  if (h.object != 0xFFFFFFFFu) {
+    Surface sf = make_surface(S, r, h, true);
+    o.param = h.param;
+    o.point[0] = sf.point.x;
+    o.point[1] = sf.point.y;
+    o.point[2] = sf.point.z;
+    o.normal[0] = sf.normal.x;
+    o.normal[1] = sf.normal.y;
+    o.normal[2] = sf.normal.z;
+    o.uv[0] = sf.u;
+    o.uv[1] = sf.v;
+    o.object = h.object;
+    o.face = sf.face;
+    o.material = sf.material;
+    o.is_internal = sf.internal ? 1u : 0u;
+  }
+  out[i] = o;
+}
+
+// Scene::SampleSky for a list of view directions (fs_sample_sky).
+__global__ void k_probe_sky(DScene S, const float* __restrict__ views, int n, float* __restrict__ rgb) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n) return;
+  V3 c = sample_sky(S, v3(views[3 * i], views[3 * i + 1], views[3 * i + 2]));
+  rgb[3 * i] = c.x;
+  rgb[3 * i + 1] = c.y;
+  rgb[3 * i + 2] = c.z;
+}
+
 // ------------------------------------------------------------------ path state
 struct PathState {
   V3 sum;  // radiance of the finished paths of this launch

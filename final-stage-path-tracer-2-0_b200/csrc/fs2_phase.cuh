@@ -498,7 +498,20 @@ __device__ __forceinline__ void ph_object_coop(const DScene& S, PhLane& w, const
     }
     todo &= ~__ballot_sync(FULL, served);
   }
-  if (start_mesh) ph_object<STATS, true>(S, w, r, c);
+  if (start_mesh) {
+    // (not ph_object: a second inlined copy of the primitive tests costs 8 KB of instruction cache)
+    const uint32_t oi = __ldg(S.scene_refs + w.sleaf_first + w.sleaf_i);
+    w.sleaf_i++;
+    const uint32_t root = __float_as_uint(obj_word(S, oi, 0).z);
+    if (root != 0xFFFFFFFFu) {
+      w.cur_obj = oi;
+      w.cur = root;
+      prefetch_l1(S.nodes + 2 * (size_t)root);
+      w.msp = 0;
+      w.flags |= PH_F_MESH;
+      w.st = PH_ENTER;
+    }
+  }
 }
 
 // ------------------------------------------------------------------ leaf BVH steps

@@ -565,6 +565,7 @@ struct Surface {
   float u, v;
   uint32_t material;  // index into materials[]
   uint32_t face;      // global face index (mesh), plane index (cuboid) or 0xFFFFFFFF
+  bool internal;      // the segment starts behind the surface (ObjectCollision::is_internal)
 };
 
 // reference source/math/intersect.cpp:769-778 — signed compares
@@ -640,7 +641,8 @@ __device__ __forceinline__ Surface make_surface(const DScene& S, const Ray& r, c
   // scene.cpp:238-247: plane through the hit with the hit normal; origin behind it -> flip
   float w = -dot(sf.normal, sf.point);
   float side = sf.normal.x * r.start.x + sf.normal.y * r.start.y + sf.normal.z * r.start.z + w;
-  if (side < 0.0f) sf.normal = neg(sf.normal);
+  sf.internal = side < 0.0f;
+  if (sf.internal) sf.normal = neg(sf.normal);
   return sf;
 }
 

@@ -199,7 +199,9 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #define FS2_WF_REP_RETURN 4
 #endif
 #ifndef FS2_WF_COOP_OBJ
-#define FS2_WF_COOP_OBJ 1  // scene-tree leaves: objects tested by 4 ... 32 lanes per owner (ph_object_coop)
+#define FS2_WF_COOP_OBJ 0  // 1: scene-tree leaves tested by 4 ... 32 lanes per owner (ph_object_coop).  Measured on the
+                           // 303-object scene: 146 vs 196 Mpaths/s per lane — the object loop dominates that scene, so
+                           // most lanes of a warp already sit in PH_OBJ and the shuffles only add work
 #endif
 #ifndef FS2_WF_REPEAT_MIN_OBJ
 #define FS2_WF_REPEAT_MIN_OBJ 2
@@ -282,7 +284,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
       }
     }
     // scene-tree leaves hold tens of objects (the reference's tree is shallow): stay in the phase
-    if (TREE && FS2_WF_COOP_OBJ && S.scene_root >= 0) {
+    if (TREE && FS2_WF_COOP_OBJ) {  // (TREE kernels are only launched for scenes with a scene tree)
 #pragma unroll 1
       for (int rep_ = 0; rep_ < FS2_WF_REP_OBJ_TREE; ++rep_) {
         unsigned m_ = __ballot_sync(FULL, w.st == PH_OBJ);

@@ -34,6 +34,8 @@ _SYMBOLS = {
                                C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p, C.c_void_p]),
     "fs_trace_range": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_int, C.c_int,
                                  C.c_float, C.c_float, C.POINTER(C.c_float)]),
+    "fs_trace_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "fs_sample_sky": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "fs_trace": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_uint32, C.c_uint32,
                            C.c_uint32, C.c_uint64, C.c_int]),
     "fs_film_read": (C.c_int, [C.c_void_p] + [C.c_void_p] * 6),
@@ -166,6 +168,22 @@ class Context:
         self._check(self.lib.fs_trace_range(self.handle, C.byref(cam), width, height, x, y,
                                             C.byref(r)))
         return r.value
+
+    def trace_rays(self, starts, stops):
+        """Scene::Trace for a batch of segments (fs_trace_rays): a structured array with
+        param / point / normal / uv / object / face / material / is_internal per ray."""
+        seg = np.ascontiguousarray(np.concatenate([np.asarray(starts, np.float32).reshape(-1, 3),
+                                                   np.asarray(stops, np.float32).reshape(-1, 3)], axis=1))
+        out = np.zeros(len(seg), abi.RAY_HIT_DT)
+        self._check(self.lib.fs_trace_rays(self.handle, _ptr(seg), len(seg), _ptr(out)))
+        return out
+
+    def sample_sky(self, views):
+        """Scene::SampleSky for a batch of view directions (fs_sample_sky): [n, 3] radiance."""
+        v = np.ascontiguousarray(np.asarray(views, np.float32).reshape(-1, 3))
+        out = np.zeros((len(v), 3), np.float32)
+        self._check(self.lib.fs_sample_sky(self.handle, _ptr(v), len(v), _ptr(out)))
+        return out
 
     def trace(self, cam, n_samples, first_sample=0, stride=1, seed=1, flags=0):
         self._check(self.lib.fs_trace(self.handle, C.byref(cam), first_sample, n_samples, stride,

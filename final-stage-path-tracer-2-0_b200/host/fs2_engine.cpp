@@ -2,6 +2,7 @@
 // surface used from Python.  This is where the reference's seam (source/engine.h:68-75)
 // meets the C ABI: flatten-if-dirty -> fs_scene_upload -> fs_trace / fs_first_hit ->
 // fs_film_read into the DisplayFrame's host buffers.  No tracing happens on the host.
+#include <math.h>
 #include <stddef.h>
 #include <stdio.h>
 #include <string.h>
@@ -187,6 +188,33 @@ void DisplayFrame::Reset() {  // frame.cpp:43-51
   f.device_dirty = true;
   if (state().frame == impl_.get()) state().expect_identity = false;
 }
+// frame.cpp:53-76, same operation order (running mean in float, quantiser in double)
+void DisplayFrame::WritePixel(const vector3& pixel, uint32 x, uint32 y) {
+  FrameImpl& f = *impl_;
+  if (x >= f.width || y >= f.height) return;
+  const size_t i = (size_t)y * f.width + x;
+  float* m = &f.mean[3 * i];
+  const float n0 = (float)f.count[i];
+  const float n1 = (float)(++f.count[i]);
+  const float in[3] = {pixel.x, pixel.y, pixel.z};
+  for (int k = 0; k < 3; k++) {
+    m[k] = (m[k] * n0 + in[k]) / n1;
+    float c = m[k] < 0.0f ? 0.0f : m[k] > 1.0f ? 1.0f : m[k];
+    f.rgb8[3 * i + k] = (uint8_t)(255.0 * pow((double)c, 1.0 / 2.2) + 0.5);
+  }
+  f.host_written = true;
+}
+void DisplayFrame::WritePixel(const TraceResult& result, uint32 x, uint32 y) {  // frame.cpp:78-85
+  FrameImpl& f = *impl_;
+  if (x >= f.width || y >= f.height) return;
+  WritePixel(result.color, x, y);
+  const size_t i = (size_t)y * f.width + x;
+  f.normal[3 * i] = result.normal.x;
+  f.normal[3 * i + 1] = result.normal.y;
+  f.normal[3 * i + 2] = result.normal.z;
+  f.depth[i] = result.depth;
+  f.mat_id[i] = result.material_id;
+}
 uint8* DisplayFrame::GetDisplayBuffer() { return impl_->rgb8.data(); }
 uint32 DisplayFrame::GetWidth() { return impl_->width; }
 uint32 DisplayFrame::GetHeight() { return impl_->height; }
@@ -239,6 +267,20 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
     st.frame = f;
     f->device_dirty = false;
     f->samples = 0;
+  }
+  if (f->host_written) {
+    // DisplayFrame::WritePixel changed the host buffers: the device film continues from them
+    // (sum = mean * count per pixel)
+    std::vector<float> sums((size_t)f->width * f->height * 4);
+    for (size_t i = 0; i < (size_t)f->width * f->height; i++) {
+      const float n = (float)f->count[i];
+      sums[4 * i] = f->mean[3 * i] * n;
+      sums[4 * i + 1] = f->mean[3 * i + 1] * n;
+      sums[4 * i + 2] = f->mean[3 * i + 2] * n;
+      sums[4 * i + 3] = n;
+    }
+    if (fs_film_load(st.ctx, sums.data()) != FS_OK) return fail("fs_film_load", st.ctx);
+    f->host_written = false;
   }
   fs_camera cam = to_pod(view);
   st.camera_hash = fnv(&cam, sizeof cam);
@@ -353,6 +395,53 @@ bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path) {
   return true;
 }
 
+// ---------------------------------------------------------------- single-ray queries
+int Scene::TraceRays(const ray* trajectories, int n, ObjectCollision* hit_info) {
+  if (n <= 0 || !trajectories || !hit_info) return 0;
+  TraceState& st = state();
+  if (ensure_context() || ensure_scene(this)) return -1;
+  std::vector<float> seg(6 * (size_t)n);
+  for (int i = 0; i < n; i++) {
+    const ray& r = trajectories[i];
+    float* g = &seg[6 * (size_t)i];
+    g[0] = r.start.x, g[1] = r.start.y, g[2] = r.start.z;
+    g[3] = r.stop.x, g[4] = r.stop.y, g[5] = r.stop.z;
+  }
+  std::vector<fs_ray_hit> hits((size_t)n);
+  if (fs_trace_rays(st.ctx, seg.data(), n, hits.data()) != FS_OK) return fail("fs_trace_rays", st.ctx);
+  const std::vector<Material*>& owner = impl_->flat_material_owner;
+  int n_hit = 0;
+  for (int i = 0; i < n; i++) {
+    const fs_ray_hit& h = hits[(size_t)i];
+    ObjectCollision& o = hit_info[i];
+    if (h.object == 0xFFFFFFFFu) continue;  // the record stays as the caller initialised it
+    n_hit++;
+    o.param = h.param;
+    o.point = vector3(h.point[0], h.point[1], h.point[2]);
+    o.surface_normal = vector3(h.normal[0], h.normal[1], h.normal[2]);
+    o.surface_texcoords = vector2(h.uv[0], h.uv[1]);
+    o.surface_material = h.material < owner.size() ? owner[h.material] : nullptr;
+    o.is_internal = h.is_internal != 0;
+  }
+  return n_hit;
+}
+
+bool Scene::Trace(const ray& trajectory, ObjectCollision* hit_info) {
+  return hit_info && TraceRays(&trajectory, 1, hit_info) == 1;
+}
+
+const vector3 Scene::SampleSky(uint32 /*depth*/, const vector3& view) {
+  TraceState& st = state();
+  if (ensure_context() || ensure_scene(this)) return vector3();
+  const float v[3] = {view.x, view.y, view.z};
+  float rgb[3] = {0.f, 0.f, 0.f};
+  if (fs_sample_sky(st.ctx, v, 1, rgb) != FS_OK) {
+    fail("fs_sample_sky", st.ctx);
+    return vector3();
+  }
+  return vector3(rgb[0], rgb[1], rgb[2]);
+}
+
 void TraceScene(const Camera& view, Scene* scene, DisplayFrame* output, ImagePlaneCache*) {
   TraceSamples(view, scene, output, 1);
 }
@@ -436,6 +525,27 @@ int fs2h_trace_samples(void* scene, const fs_camera* cam, void* frame, uint32_t 
 }
 float fs2h_trace_range(void* scene, const fs_camera* cam, void* frame, float x, float y) {
   return base::TraceRange(from_pod(cam), (base::Scene*)scene, (base::DisplayFrame*)frame, x, y);
+}
+// Scene::Trace / SampleSky / DisplayFrame::WritePixel through the mirror (tests).
+// out: param, point xyz, normal xyz, uv, material id, is_internal  (11 floats); returns hit.
+int fs2h_scene_trace(void* scene, const float* start, const float* stop, float* out) {
+  base::ray r(base::vector3(start[0], start[1], start[2]), base::vector3(stop[0], stop[1], stop[2]));
+  base::ObjectCollision c;
+  bool hit = ((base::Scene*)scene)->Trace(r, &c);
+  out[0] = c.param;
+  out[1] = c.point.x, out[2] = c.point.y, out[3] = c.point.z;
+  out[4] = c.surface_normal.x, out[5] = c.surface_normal.y, out[6] = c.surface_normal.z;
+  out[7] = c.surface_texcoords.x, out[8] = c.surface_texcoords.y;
+  out[9] = c.surface_material ? (float)c.surface_material->GetID() : -1.0f;
+  out[10] = c.is_internal ? 1.0f : 0.0f;
+  return hit ? 1 : 0;
+}
+void fs2h_scene_sample_sky(void* scene, const float* view, float* rgb) {
+  base::vector3 c = ((base::Scene*)scene)->SampleSky(0, base::vector3(view[0], view[1], view[2]));
+  rgb[0] = c.x, rgb[1] = c.y, rgb[2] = c.z;
+}
+void fs2h_frame_write_pixel(void* f, const float* rgb, uint32_t x, uint32_t y) {
+  ((base::DisplayFrame*)f)->WritePixel(base::vector3(rgb[0], rgb[1], rgb[2]), x, y);
 }
 void fs2h_set_device(int device) { base::SetTraceDevice(device); }
 void fs2h_set_devices(const int* devices, int n) { base::SetTraceDevices(devices, n); }

@@ -57,6 +57,14 @@ struct vector4 {
 };
 typedef vector4 plane;
 
+// reference source/math/trace.h:40-54 (the part the tracing API needs)
+struct ray {
+  vector3 start, stop, dir;
+  ray(const vector3& init_start, const vector3& init_stop)
+      : start(init_start), stop(init_stop),
+        dir(init_stop.x - init_start.x, init_stop.y - init_start.y, init_stop.z - init_start.z) {}
+};
+
 // ---------------------------------------------------------------- camera
 class Camera {
  public:
@@ -189,6 +197,28 @@ class MeshObject : public Object {
              const vector4& rotation = vector4(0, 0, 0, 0));
 };
 
+// reference source/object.h:47-61
+class Material;
+struct ObjectCollision {
+  float32 param;              // 2.0 (collision ctor, trace.cpp:18-21) when nothing was hit
+  vector3 point;
+  vector3 surface_normal;
+  vector2 surface_texcoords;
+  Material* surface_material;
+  bool is_internal;
+  ObjectCollision() : param(2.0f), surface_material(nullptr), is_internal(false) {}
+};
+
+// reference source/frame.h:40-47
+struct TraceResult {
+  vector3 color;
+  vector3 normal;
+  float32 depth;
+  uint64 material_id;
+  uint64 ray_count;
+  TraceResult() : depth(0.0f), material_id(0), ray_count(0) {}
+};
+
 // ---------------------------------------------------------------- scene
 class Scene {
  public:
@@ -209,11 +239,18 @@ class Scene {
   QuadObject* AddQuadObject(const vector3& position, const vector3& u, const vector3& v);
   void SetSkyMaterial(std::shared_ptr<LightMaterial> material);
   LightMaterial* GetSkyMaterial();
+  // One ray against the scene on the device (fs_trace_rays; scene.cpp:227-249).  A single ray
+  // per call pays a launch and two copies: for many rays use TraceRays below.
+  bool Trace(const ray& trajectory, ObjectCollision* hit_info);
+  // Sky radiance seen along `view` (fs_sample_sky; scene.cpp:157-162).
+  const vector3 SampleSky(uint32 depth, const vector3& view);
   void Optimize();
   uint32 GetCameraCount();
   Camera* GetCamera(uint32 index);
 
   // ---- additions for the GPU path
+  // Batched Scene::Trace: n rays, hit_info[i] filled like Trace(); returns the number of hits.
+  int TraceRays(const ray* trajectories, int n, ObjectCollision* hit_info);
   // Flattens objects, octrees, materials, textures and the normal table into the arrays
   // of include/fs2_cabi.h.  The returned description stays valid until the scene changes.
   const fs_scene_desc* Flatten();
@@ -232,6 +269,10 @@ class DisplayFrame {
   DisplayFrame(uint32 width, uint32 height);
   ~DisplayFrame();
   void Reset();
+  // frame.cpp:53-85: running mean, count and display byte of one pixel, on the host buffers;
+  // the next TraceScene / TraceSamples call uploads the frame before it adds its samples.
+  void WritePixel(const vector3& pixel, uint32 x, uint32 y);
+  void WritePixel(const TraceResult& result, uint32 x, uint32 y);
   uint8* GetDisplayBuffer();
   uint32 GetWidth();
   uint32 GetHeight();

@@ -45,6 +45,7 @@ struct SceneImpl {
   uint64_t flat_version = 0;
   FlatArrays flat;
   fs_scene_desc desc;
+  std::vector<base::Material*> flat_material_owner;  // flattened material index -> object
 };
 
 struct FrameImpl {
@@ -56,6 +57,7 @@ struct FrameImpl {
   uint32_t samples = 0;  // samples accumulated since the last Reset()
   bool device_dirty = true;  // device film must be cleared before the next launch
   bool pinned = false;       // buffers are page-locked (fs_host_register)
+  bool host_written = false; // WritePixel changed the host buffers: upload before the next launch
 };
 
 inline Vec3 to3(const base::vector3& v) { return Vec3(v.x, v.y, v.z); }

@@ -256,7 +256,8 @@ bool Scene::LoadScene(const std::string& filename) {
 }
 
 // ---------------------------------------------------------------- flatten
-static uint32_t flatten_material(FlatArrays* F, std::map<Material*, uint32_t>* seen, Material* m) {
+static uint32_t flatten_material(FlatArrays* F, std::map<Material*, uint32_t>* seen, Material* m,
+                                 std::vector<Material*>* owner) {
   if (!m) return 0xFFFFFFFFu;
   auto it = seen->find(m);
   if (it != seen->end()) return it->second;
@@ -274,6 +275,7 @@ static uint32_t flatten_material(FlatArrays* F, std::map<Material*, uint32_t>* s
   }
   uint32_t idx = (uint32_t)F->materials.size();
   F->materials.push_back(r);
+  owner->push_back(m);
   (*seen)[m] = idx;
   return idx;
 }
@@ -283,6 +285,7 @@ const fs_scene_desc* Scene::Flatten() {
   if (S->flat_valid) return &S->desc;
   FlatArrays& F = S->flat;
   F = FlatArrays();
+  S->flat_material_owner.clear();
   std::map<Material*, uint32_t> seen;
   unsigned threads = std::thread::hardware_concurrency();
   if (const char* e = getenv("FS2_HOST_THREADS")) threads = (unsigned)atoi(e);
@@ -292,7 +295,7 @@ const fs_scene_desc* Scene::Flatten() {
     Object* o = up.get();
     ObjectImpl* oi = o->impl();
     fs_object r = oi->rec;
-    r.material = flatten_material(&F, &seen, o->GetMaterial());
+    r.material = flatten_material(&F, &seen, o->GetMaterial(), &S->flat_material_owner);
     put3(r.bmin, oi->box.mn);
     put3(r.bmax, oi->box.mx);
     boxes.push_back(oi->box);
@@ -318,7 +321,7 @@ const fs_scene_desc* Scene::Flatten() {
     }
     F.objects.push_back(r);
   }
-  F.sky = flatten_material(&F, &seen, S->sky.get());
+  F.sky = flatten_material(&F, &seen, S->sky.get(), &S->flat_material_owner);
   F.scene_root = S->tree_valid ? build_scene_tree(boxes, &F) : -1;
   F.lut = normal_table();
 

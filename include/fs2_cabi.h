@@ -267,6 +267,29 @@ int fs_first_hit(fs_ctx* ctx, const fs_camera* cam, int width, int height,
 int fs_trace_range(fs_ctx* ctx, const fs_camera* cam, int width, int height,
                    float x, float y, float* range);
 
+/* One ray query as Scene::Trace leaves its ObjectCollision (reference source/object.h:47-61,
+ * source/scene.cpp:227-249: nearest hit, then the back-face flip of the normal). */
+typedef struct fs_ray_hit {
+  float param;          /* portion of the segment, FS_NO_HIT_PARAM when nothing was hit */
+  float point[3];
+  float normal[3];      /* flipped towards the ray origin when struck from behind */
+  float uv[2];
+  uint32_t object;      /* index into objects[], 0xFFFFFFFF = none */
+  uint32_t face;        /* mesh face / cuboid plane, 0xFFFFFFFF otherwise */
+  uint32_t material;    /* index into materials[] (sky_material when nothing was hit) */
+  uint32_t is_internal; /* 1 when the origin lies behind the surface (scene.cpp:244-247) */
+} fs_ray_hit;
+
+/* Replaces Scene::Trace(const ray&, ObjectCollision*) (reference source/scene.h:128,
+ * source/scene.cpp:227-249) for n_rays segments at once: segments[6*i..] = start xyz, stop xyz.
+ * Host pointers. */
+int fs_trace_rays(fs_ctx* ctx, const float* segments, int n_rays, fs_ray_hit* out);
+
+/* Replaces Scene::SampleSky(depth, view) (reference source/scene.h:131, source/scene.cpp:157-162)
+ * for n view directions (3 floats each); rgb gets 3 floats per query.  The reference's `depth`
+ * argument does not reach LightMaterial::Sample's result and is not part of the call. */
+int fs_sample_sky(fs_ctx* ctx, const float* views, int n, float* rgb);
+
 /* Replaces n_samples calls of TraceScene (engine.cpp:253-296): accumulates
  * samples first_sample, first_sample+stride, ... (n_samples of them) of every
  * pixel into the device film.  Per-sample random streams depend only on

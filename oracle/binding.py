@@ -81,6 +81,34 @@ def first_hit(scene, cam, w, h):
     return out
 
 
+def trace_rays(scene, starts, stops):
+    """Oracle Scene::Trace for explicit segments -> dict of arrays (fs_trace_rays' fields)."""
+    seg = np.ascontiguousarray(np.concatenate([np.asarray(starts, np.float32).reshape(-1, 3),
+                                               np.asarray(stops, np.float32).reshape(-1, 3)], axis=1))
+    n = len(seg)
+    out = {"param": np.zeros(n, np.float32), "point": np.zeros((n, 3), np.float32),
+           "normal": np.zeros((n, 3), np.float32), "uv": np.zeros((n, 2), np.float32),
+           "object": np.zeros(n, np.uint32), "face": np.zeros(n, np.uint32),
+           "material": np.zeros(n, np.uint32), "is_internal": np.zeros(n, np.uint32)}
+    d = scene.desc()
+    rc = lib().fs2o_trace_rays(C.byref(d), _p(seg), n, _p(out["param"]), _p(out["point"]),
+                               _p(out["normal"]), _p(out["uv"]), _p(out["object"]), _p(out["face"]),
+                               _p(out["material"]), _p(out["is_internal"]))
+    if rc != 0:
+        raise RuntimeError("fs2o_trace_rays failed: %d" % rc)
+    return out
+
+
+def sample_sky(scene, views):
+    v = np.ascontiguousarray(np.asarray(views, np.float32).reshape(-1, 3))
+    out = np.zeros((len(v), 3), np.float32)
+    d = scene.desc()
+    rc = lib().fs2o_sample_sky(C.byref(d), _p(v), len(v), _p(out))
+    if rc != 0:
+        raise RuntimeError("fs2o_sample_sky failed: %d" % rc)
+    return out
+
+
 def ref_seed_schedule(frames, clock0=1700000000000):
     """The scripted per-frame clock of oracle/ref/harness.cpp (render())."""
     return np.array([clock0 + 1000 * k + 7 * k * k for k in range(frames)], np.uint64)

@@ -32,6 +32,7 @@ def test_struct_sizes_match_header():
     assert C.sizeof(abi.fs_stats) == 88
     assert C.sizeof(abi.fs_scene_desc) == 56 + 10 * 8
     assert abi.NODE_DT.itemsize == 32 and abi.OBJECT_DT.itemsize == 144
+    assert abi.RAY_HIT_DT.itemsize == 52  # fs_ray_hit
 
 
 def test_no_device_fails_loudly():
