@@ -467,7 +467,10 @@ def run_gpu(args, cfg, rank, world, local_rank):
             store.wait(["fs2_e2e_done"], datetime.timedelta(minutes=20))
     barrier()
     n_px = W * H
-    d2h = n_px * (12 + 4 + 3 + 12 + 4 + 8)  # mean, count, rgb8, normal, depth, material id
+    # what TraceSamples copies back per call: the picture (float mean, count, display bytes).  The
+    # guide planes (normal, depth, material id: 24 more bytes per pixel, private in the reference's
+    # DisplayFrame) stay on the device until a getter asks for them.
+    d2h = n_px * (12 + 4 + 3)
 
     if rank == 0:
         e2e_value = float(W) * H * SPP / median(e2e_s[1:]) / 1e6

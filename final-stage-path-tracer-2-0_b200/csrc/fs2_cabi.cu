@@ -50,6 +50,7 @@ struct fs_ctx {
   char error[512] = "";
   // scene
   bool have_scene = false;
+  DeviceBuf sref_sphere;  // per scene ref: centre + radius of a sphere, NaN radius otherwise
   DeviceBuf nodes, scene_refs, tri_plane, tri_aux, faces, objects, materials, textures, texels,
       lut, lb_nodes, lb_leaf, lb_plane, lb_aux, lb_order;
   DScene ds;
@@ -546,6 +547,26 @@ int scene_upload_one(fs_ctx* ctx, const fs_scene_desc* s, const std::vector<floa
     CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));  // `tagged` is pageable and dies here
   }
   if ((rc = dev_upload(ctx, &ctx->scene_refs, s->scene_refs, (size_t)s->n_scene_refs * 4))) return rc;
+  {
+    // Scene-tree leaves list their objects by index; most of a many-object scene's are spheres.
+    // A copy of centre and radius beside every reference lets the leaf loop test a sphere from one
+    // 16-byte load instead of the reference -> object header -> payload chain (same float values,
+    // same sphere test).
+    std::vector<float> sph(4 * (size_t)s->n_scene_refs + 4);
+    for (uint32_t k = 0; k < s->n_scene_refs; k++) {
+      const fs_object& o = s->objects[s->scene_refs[k]];
+      float* q = &sph[4 * (size_t)k];
+      if (o.type == FS_OBJ_SPHERE) {
+        q[0] = o.f[0], q[1] = o.f[1], q[2] = o.f[2], q[3] = o.f[3];
+        if (!(q[3] == q[3])) q[3] = NAN;  // (a NaN radius takes the generic path: same outcome)
+      } else {
+        q[0] = q[1] = q[2] = 0.f;
+        q[3] = NAN;
+      }
+    }
+    if ((rc = dev_upload(ctx, &ctx->sref_sphere, sph.data(), sph.size() * 4))) return rc;
+    CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  }
   if ((rc = dev_upload(ctx, &ctx->tri_plane, s->tri_plane, (size_t)s->n_tris * 16))) return rc;
   if ((rc = dev_upload(ctx, &ctx->tri_aux, s->tri_aux, (size_t)s->n_tris * sizeof(fs_tri_aux)))) return rc;
   if ((rc = dev_upload(ctx, &ctx->faces, s->faces, (size_t)s->n_faces * sizeof(fs_face_attr)))) return rc;
@@ -558,6 +579,7 @@ int scene_upload_one(fs_ctx* ctx, const fs_scene_desc* s, const std::vector<floa
   DScene& d = ctx->ds;
   d.nodes = (const float4*)ctx->nodes.p;
   d.scene_refs = (const uint32_t*)ctx->scene_refs.p;
+  d.sref_sphere = (const float4*)ctx->sref_sphere.p;
   d.tri_plane = (const float4*)ctx->tri_plane.p;
   d.tri_aux = (const float4*)ctx->tri_aux.p;
   d.faces = (const float4*)ctx->faces.p;
@@ -744,7 +766,7 @@ int fs_destroy(fs_ctx* ctx) {
   ctx->peers.clear();
   cudaSetDevice(ctx->device);
   cudaStreamSynchronize(ctx->stream);
-  DeviceBuf* all[] = {&ctx->nodes, &ctx->scene_refs, &ctx->tri_plane, &ctx->tri_aux, &ctx->faces,
+  DeviceBuf* all[] = {&ctx->sref_sphere, &ctx->nodes, &ctx->scene_refs, &ctx->tri_plane, &ctx->tri_aux, &ctx->faces,
                       &ctx->objects, &ctx->materials, &ctx->textures, &ctx->texels, &ctx->lut,
                       &ctx->lb_nodes, &ctx->lb_leaf, &ctx->lb_plane, &ctx->lb_aux, &ctx->lb_order,
                       &ctx->sum, &ctx->aux, &ctx->mat_id, &ctx->mean, &ctx->count, &ctx->rgb8,

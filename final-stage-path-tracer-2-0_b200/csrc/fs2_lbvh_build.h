@@ -23,6 +23,9 @@ namespace fs2 {
 
 // Leaves with fewer triangles than this are scanned directly (one node, no tree).
 #define FS2_LBVH_MAX_LEVELS 7  // 4^(7+1) = 65 536 triangles per octree leaf
+#ifndef FS2_LBVH_SAH_STEP
+#define FS2_LBVH_SAH_STEP 1u  // order 3: cut positions are multiples of this many records
+#endif
 #ifndef FS2_LBVH_SAH_MAX
 #define FS2_LBVH_SAH_MAX 4096u  // order 2: ranges up to this size try all three cut axes
 #endif
@@ -453,7 +456,11 @@ struct SahLeafBuilder {
   std::vector<uint32_t>& perm;   // positions -> record (local index)
   std::vector<LbNode>& nodes;    // local node array, root = 0, child links local
   uint32_t first;                // first record of the leaf in the permuted arrays
-  std::vector<uint32_t> tmp, keep;
+  struct Keyed {
+    float key;
+    uint32_t rec;
+  };
+  std::vector<Keyed> keyed;
   std::vector<double> rarea;
 
   static double area(const Box3& b) {
@@ -500,31 +507,42 @@ struct SahLeafBuilder {
       std::nth_element(perm.begin() + lo, perm.begin() + lo + k, perm.begin() + hi, less_on(ax));
       return lo + k;
     }
+    // full sweep over the three centre orders; (key, record) pairs are sorted in place of an
+    // indirect comparison (the build's time is these sorts)
     double best = INFINITY;
     uint32_t best_k = kmin;
-    tmp.assign(perm.begin() + lo, perm.begin() + hi);
+    int best_ax = -1;
+    keyed.resize(n);
     rarea.resize(n + 1);
+    auto sort_on = [&](int ax) {
+      for (uint32_t i = 0; i < n; i++) keyed[i] = Keyed{cen[3 * (size_t)perm[lo + i] + ax], perm[lo + i]};
+      std::sort(keyed.begin(), keyed.end(),
+                [](const Keyed& a, const Keyed& b) { return a.key < b.key || (a.key == b.key && a.rec < b.rec); });
+    };
     for (int ax = 0; ax < 3; ax++) {
-      std::sort(tmp.begin(), tmp.end(), less_on(ax));
+      sort_on(ax);
       Box3 b;
       b.reset();
       for (uint32_t i = n; i-- > 0;) {
-        b.add(boxes[tmp[i]]);
+        b.add(boxes[keyed[i].rec]);
         rarea[i] = area(b);
       }
       b.reset();
       for (uint32_t k = 1; k <= kmax; k++) {
-        b.add(boxes[tmp[k - 1]]);
+        b.add(boxes[keyed[k - 1].rec]);
         if (k < kmin || (step > 1 && k % step)) continue;
         double cost = area(b) * ((k + 3) / 4) + rarea[k] * ((n - k + 3) / 4);
         if (cost < best) {
           best = cost;
           best_k = k;
-          keep = tmp;
+          best_ax = ax;
         }
       }
     }
-    if (best < INFINITY) std::copy(keep.begin(), keep.end(), perm.begin() + lo);
+    if (best_ax >= 0) {
+      if (best_ax != 2) sort_on(best_ax);  // (a total order: the same permutation as before)
+      for (uint32_t i = 0; i < n; i++) perm[lo + i] = keyed[i].rec;
+    }
     return lo + best_k;
   }
   // orders the <= 16 records of a quad-level node into groups of four
@@ -564,7 +582,7 @@ struct SahLeafBuilder {
     const uint64_t cc = cap(levels - 1);  // most records a child may hold
     auto lim = [](uint64_t v) { return (uint32_t)(v > 0xFFFFFFFFull ? 0xFFFFFFFFull : v); };
     // first cut: both halves must fit two children
-    uint32_t mid = split(lo, hi, n > 2 * cc ? lim(n - 2 * cc) : 1, lim(2 * cc), 1);
+    uint32_t mid = split(lo, hi, n > 2 * cc ? lim(n - 2 * cc) : 1, lim(2 * cc), FS2_LBVH_SAH_STEP);
     uint32_t r[5] = {lo, lo, mid, mid, hi};
     auto half = [&](uint32_t a, uint32_t b, uint32_t& m) {
       uint32_t h = b - a;
@@ -572,7 +590,7 @@ struct SahLeafBuilder {
         m = b;  // one child only
         return;
       }
-      m = split(a, b, h > cc ? lim(h - cc) : 1, lim(cc), 1);
+      m = split(a, b, h > cc ? lim(h - cc) : 1, lim(cc), FS2_LBVH_SAH_STEP);
     };
     half(lo, mid, r[1]);
     half(mid, hi, r[3]);
@@ -617,7 +635,7 @@ inline std::vector<LbNode> build_leaf_sah(const fs_scene_desc* s, const LeafJob&
   int levels = 0;
   while (SahLeafBuilder::cap(levels) < n) levels++;
   levels = levels + 2 < FS2_LBVH_MAX_LEVELS - 1 ? levels + 2 : FS2_LBVH_MAX_LEVELS - 1;
-  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}, {}};
+  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}};
   b.build(0, 0, n, levels);
   if (nodes.size() >= 65536) return {};  // stack entries carry 16-bit node offsets
   for (uint32_t i = 0; i < n; i++) {

@@ -54,6 +54,12 @@ static inline unsigned ph_smem_bytes(bool scene_tree) {
 #define FS2_PH_FUSE_DONE 1  // a walk that ends (root miss, last frame popped) leaves the tree in the same step
 #endif
 
+#ifndef FS2_PH_EARLY_ROOT
+#define FS2_PH_EARLY_ROOT 1  // measured: config 2 709 -> 723, grid4m 606 -> 614 Mpaths/s
+#endif
+#ifndef FS2_PH_SPHERE_FAST
+#define FS2_PH_SPHERE_FAST 1  // scene-tree leaves test spheres from DScene::sref_sphere
+#endif
 #ifndef FS2_PH_SKIP_EMPTY
 #define FS2_PH_SKIP_EMPTY 1  // children that are empty leaves are answered from the parent's occupancy byte
 #endif
@@ -164,6 +170,11 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
                                          const PhSmem& sm, Counters& c) {
   const bool mesh = !TREE || (w.flags & PH_F_MESH) != 0;  // without a scene tree only meshes walk
   NodeRec n = load_node(S, w.cur);
+#if FS2_PH_EARLY_ROOT
+  // the leaf-BVH root of a mesh leaf, fetched beside the node instead of after its box test
+  // (one memory round trip less per leaf visit; wasted for internal nodes and misses)
+  const uint32_t early_root = mesh ? __ldg(&S.lb_leaf[w.cur].x) : 0u;
+#endif
   float nparam;
   V3 entry = r.start;
   bool inside;
@@ -186,7 +197,11 @@ __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& 
       w.st = PH_OBJ;
     } else {
       // mesh leaf (mesh.cpp:86-111)
+#if FS2_PH_EARLY_ROOT
+      uint32_t root = early_root;
+#else
       uint32_t root = __ldg(&S.lb_leaf[w.cur].x);
+#endif
       if (r.zero_length || (w.flags & PH_F_FAR) || (root == 0xFFFFFFFFu && n.count > 16u)) {
         // rare: point query / far-away origin / leaf beyond the BVH level cap -> linear scan in
         // reference order
@@ -363,8 +378,30 @@ __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray&
     w.st = PH_RETURN;
     return;
   }
-  const uint32_t oi = __ldg(S.scene_refs + w.sleaf_first + w.sleaf_i);
+  const uint32_t k = w.sleaf_first + w.sleaf_i;
   w.sleaf_i++;
+#if FS2_PH_SPHERE_FAST
+  {
+    // spheres (most of what a many-object scene lists) are tested from the 16-byte copy of their
+    // centre and radius that sits beside the reference: one load, no dependent chain
+    const float4 sp = __ldg(S.sref_sphere + k);
+    if (sp.w == sp.w) {
+      if (STATS) c.n_prim++;
+      float t;
+      if (sphere_test(v3(sp.x, sp.y, sp.z), sp.w, r, t) && t < w.rec.param) {
+        w.rec.param = t;
+        w.rec.object = __ldg(S.scene_refs + k);
+        w.rec.prim = 0xFFFFFFFFu;
+        if (w.rec.param < w.glob.param) {
+          w.glob = w.rec;
+          w.flags |= PH_F_SIMPROVED;
+        }
+      }
+      return;
+    }
+  }
+#endif
+  const uint32_t oi = __ldg(S.scene_refs + k);
   float4 w0 = obj_word(S, oi, 0);
   if (__float_as_uint(w0.x) == FS_OBJ_MESH) {
     uint32_t root = __float_as_uint(w0.z);

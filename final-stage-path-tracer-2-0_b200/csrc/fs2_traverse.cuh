@@ -16,6 +16,7 @@ namespace fs2 {
 struct DScene {
   const float4* nodes;      // 2 x float4 per fs_node
   const uint32_t* scene_refs;
+  const float4* sref_sphere;  // per scene ref: sphere centre xyz + radius, or a NaN radius (fs2_cabi.cu)
   const float4* tri_plane;  // 1 x float4 per packed triangle
   const float4* tri_aux;    // 3 x float4 per fs_tri_aux
   const float4* faces;      // 4 x float4 per fs_face_attr

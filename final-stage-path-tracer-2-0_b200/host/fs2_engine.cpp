@@ -84,9 +84,12 @@ void fail_msg(const char* msg) {
   fprintf(stderr, "fs2: %s\n", st.error);
 }
 
+void fetch_aux(fs2h::FrameImpl* f);
+
 int ensure_context() {
   TraceState& st = state();
   if (st.ctx && st.ctx_device == st.device && !st.devices_changed) return 0;
+  if (st.ctx && st.frame) fetch_aux((fs2h::FrameImpl*)const_cast<void*>(st.frame));
   if (st.ctx) fs_destroy(st.ctx);
   st.ctx = nullptr;
   st.scene = nullptr;
@@ -115,6 +118,18 @@ int ensure_scene(base::Scene* scene) {
   st.scene_version = si->flat_version;
   st.scene_hash = hash_scene(d);
   return 0;
+}
+
+// The guide planes (normal, depth, material id: private in the reference, frame.h:86-91) are
+// fetched from the device when somebody reads them, not after every TraceScene: they are 50 of
+// the 89 MB a 1080p frame would otherwise move per call.
+void fetch_aux(fs2h::FrameImpl* f) {
+  TraceState& st = state();
+  if (!f || !f->aux_stale) return;
+  f->aux_stale = false;
+  if (!st.ctx || st.frame != f) return;
+  if (fs_film_read(st.ctx, nullptr, nullptr, nullptr, f->normal.data(), f->depth.data(), f->mat_id.data()) != FS_OK)
+    fail("fs_film_read", st.ctx);
 }
 
 fs_camera to_pod(const base::Camera& c) {
@@ -186,6 +201,8 @@ void DisplayFrame::Reset() {  // frame.cpp:43-51
   std::fill(f.mat_id.begin(), f.mat_id.end(), (uint64_t)0);
   f.samples = 0;
   f.device_dirty = true;
+  f.aux_stale = false;
+  f.host_written = false;
   if (state().frame == impl_.get()) state().expect_identity = false;
 }
 // frame.cpp:53-76, same operation order (running mean in float, quantiser in double)
@@ -222,9 +239,18 @@ float32 DisplayFrame::GetAspectRatio() { return (float32)impl_->width / impl_->h
 void DisplayFrame::SetFrameCount(uint32 count) { impl_->frame_count = count; }
 const float32* DisplayFrame::GetRenderTarget() { return impl_->mean.data(); }
 const uint32* DisplayFrame::GetCountBuffer() { return impl_->count.data(); }
-const float32* DisplayFrame::GetNormalBuffer() { return impl_->normal.data(); }
-const float32* DisplayFrame::GetDepthBuffer() { return impl_->depth.data(); }
-const uint64* DisplayFrame::GetMaterialIdBuffer() { return impl_->mat_id.data(); }
+const float32* DisplayFrame::GetNormalBuffer() {
+  fetch_aux(impl_.get());
+  return impl_->normal.data();
+}
+const float32* DisplayFrame::GetDepthBuffer() {
+  fetch_aux(impl_.get());
+  return impl_->depth.data();
+}
+const uint64* DisplayFrame::GetMaterialIdBuffer() {
+  fetch_aux(impl_.get());
+  return impl_->mat_id.data();
+}
 
 // ---------------------------------------------------------------- tracing
 void SetTraceDevice(int device) {
@@ -253,6 +279,7 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
   TraceState& st = state();
   if (ensure_context() || ensure_scene(scene)) return -1;
   FrameImpl* f = output->impl();
+  if (st.frame && st.frame != f) fetch_aux((FrameImpl*)const_cast<void*>(st.frame));  // the device film changes hands
   if (st.film_w != f->width || st.film_h != f->height) {
     if (fs_film_resize(st.ctx, (int)f->width, (int)f->height) != FS_OK)
       return fail("fs_film_resize", st.ctx);
@@ -299,9 +326,9 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
     return fail("fs_trace", st.ctx);
   f->samples += n_samples;
   f->frame_count += n_samples;
-  if (fs_film_read(st.ctx, f->mean.data(), f->count.data(), f->rgb8.data(), f->normal.data(),
-                   f->depth.data(), f->mat_id.data()) != FS_OK)
+  if (fs_film_read(st.ctx, f->mean.data(), f->count.data(), f->rgb8.data(), nullptr, nullptr, nullptr) != FS_OK)
     return fail("fs_film_read", st.ctx);
+  f->aux_stale = true;
   return 0;
 }
 
