@@ -453,16 +453,34 @@ inline void build_leaf(const fs_scene_desc* s, const LeafJob& job, LbvhHost* out
 struct SahLeafBuilder {
   const std::vector<Box3>& boxes;
   const std::vector<float>& cen;
-  std::vector<uint32_t>& perm;   // positions -> record (local index)
+  std::vector<uint32_t>& perm;   // positions -> record (local index); = ord[0] when the build ends
   std::vector<LbNode>& nodes;    // local node array, root = 0, child links local
   uint32_t first;                // first record of the leaf in the permuted arrays
-  struct Keyed {
-    float key;
-    uint32_t rec;
-  };
-  std::vector<Keyed> keyed;
+  // The records in each of the three centre orders (ties by record index).  Every range [lo, hi)
+  // of a node holds the same records in all three; a cut marks its left side and partitions the
+  // other two orders stably, so they stay sorted and no split ever sorts again.
+  std::vector<uint32_t> ord[3];
+  std::vector<uint32_t> tmp;
+  std::vector<uint8_t> left;
   std::vector<double> rarea;
 
+  void presort() {
+    const uint32_t n = (uint32_t)perm.size();
+    struct Keyed {
+      float key;
+      uint32_t rec;
+    };
+    std::vector<Keyed> keyed(n);
+    for (int ax = 0; ax < 3; ax++) {
+      for (uint32_t i = 0; i < n; i++) keyed[i] = Keyed{cen[3 * (size_t)i + ax], i};
+      std::sort(keyed.begin(), keyed.end(),
+                [](const Keyed& a, const Keyed& b) { return a.key < b.key || (a.key == b.key && a.rec < b.rec); });
+      ord[ax].resize(n);
+      for (uint32_t i = 0; i < n; i++) ord[ax][i] = keyed[i].rec;
+    }
+    left.assign(n, 0);
+    tmp.resize(n);
+  }
   static double area(const Box3& b) {
     double x = (double)b.hi[0] - b.lo[0], y = (double)b.hi[1] - b.lo[1], z = (double)b.hi[2] - b.lo[2];
     double v = x * y + y * z + z * x;
@@ -471,11 +489,11 @@ struct SahLeafBuilder {
   Box3 range_box(uint32_t lo, uint32_t hi) const {
     Box3 b;
     b.reset();
-    for (uint32_t i = lo; i < hi; i++) b.add(boxes[perm[i]]);
+    for (uint32_t i = lo; i < hi; i++) b.add(boxes[ord[0][i]]);
     return b;
   }
-  // Cuts perm[lo, hi) into [lo, mid) and [mid, hi) with kmin <= mid - lo <= kmax (and both sides
-  // non-empty); `step` restricts the left size to multiples of it (group alignment).
+  // Cuts the range [lo, hi) into [lo, mid) and [mid, hi) with kmin <= mid - lo <= kmax (and both
+  // sides non-empty); `step` restricts the left size to multiples of it (group alignment).
   uint32_t split(uint32_t lo, uint32_t hi, uint32_t kmin, uint32_t kmax, uint32_t step) {
     const uint32_t n = hi - lo;
     if (kmin < 1) kmin = 1;
@@ -485,64 +503,56 @@ struct SahLeafBuilder {
       kmax = kmax / step * step;
     }
     if (kmin > kmax) return lo + (n + 1) / 2;  // cannot happen for feasible budgets
-    auto less_on = [this](int ax) {
-      return [this, ax](uint32_t a, uint32_t b) {
-        float va = cen[3 * (size_t)a + ax], vb = cen[3 * (size_t)b + ax];
-        return va < vb || (va == vb && a < b);
-      };
-    };
-    if (n > FS2_LBVH_SAH_MAX) {
-      float mn[3] = {INFINITY, INFINITY, INFINITY}, mx[3] = {-INFINITY, -INFINITY, -INFINITY};
-      for (uint32_t i = lo; i < hi; i++)
-        for (int k = 0; k < 3; k++) {
-          float v = cen[3 * (size_t)perm[i] + k];
-          mn[k] = fminf(mn[k], v);
-          mx[k] = fmaxf(mx[k], v);
-        }
-      int ax = 0;
-      if (mx[1] - mn[1] > mx[ax] - mn[ax]) ax = 1;
-      if (mx[2] - mn[2] > mx[ax] - mn[ax]) ax = 2;
-      uint32_t k = (n / 2 + step - 1) / step * step;
-      k = k < kmin ? kmin : k > kmax ? kmax : k;
-      std::nth_element(perm.begin() + lo, perm.begin() + lo + k, perm.begin() + hi, less_on(ax));
-      return lo + k;
-    }
-    // full sweep over the three centre orders; (key, record) pairs are sorted in place of an
-    // indirect comparison (the build's time is these sorts)
-    double best = INFINITY;
+    int best_ax = 0;
     uint32_t best_k = kmin;
-    int best_ax = -1;
-    keyed.resize(n);
-    rarea.resize(n + 1);
-    auto sort_on = [&](int ax) {
-      for (uint32_t i = 0; i < n; i++) keyed[i] = Keyed{cen[3 * (size_t)perm[lo + i] + ax], perm[lo + i]};
-      std::sort(keyed.begin(), keyed.end(),
-                [](const Keyed& a, const Keyed& b) { return a.key < b.key || (a.key == b.key && a.rec < b.rec); });
-    };
-    for (int ax = 0; ax < 3; ax++) {
-      sort_on(ax);
-      Box3 b;
-      b.reset();
-      for (uint32_t i = n; i-- > 0;) {
-        b.add(boxes[keyed[i].rec]);
-        rarea[i] = area(b);
-      }
-      b.reset();
-      for (uint32_t k = 1; k <= kmax; k++) {
-        b.add(boxes[keyed[k - 1].rec]);
-        if (k < kmin || (step > 1 && k % step)) continue;
-        double cost = area(b) * ((k + 3) / 4) + rarea[k] * ((n - k + 3) / 4);
-        if (cost < best) {
-          best = cost;
-          best_k = k;
-          best_ax = ax;
+    if (n > FS2_LBVH_SAH_MAX) {
+      // median of the longest axis of the centres
+      float ext[3];
+      for (int ax = 0; ax < 3; ax++)
+        ext[ax] = cen[3 * (size_t)ord[ax][hi - 1] + ax] - cen[3 * (size_t)ord[ax][lo] + ax];
+      if (ext[1] > ext[best_ax]) best_ax = 1;
+      if (ext[2] > ext[best_ax]) best_ax = 2;
+      uint32_t k = (n / 2 + step - 1) / step * step;
+      best_k = k < kmin ? kmin : k > kmax ? kmax : k;
+    } else {
+      double best = INFINITY;
+      rarea.resize(n + 1);
+      for (int ax = 0; ax < 3; ax++) {
+        const uint32_t* o = ord[ax].data() + lo;
+        Box3 b;
+        b.reset();
+        for (uint32_t i = n; i-- > 0;) {
+          b.add(boxes[o[i]]);
+          rarea[i] = area(b);
+        }
+        b.reset();
+        for (uint32_t k = 1; k <= kmax; k++) {
+          b.add(boxes[o[k - 1]]);
+          if (k < kmin || (step > 1 && k % step)) continue;
+          double cost = area(b) * ((k + 3) / 4) + rarea[k] * ((n - k + 3) / 4);
+          if (cost < best) {
+            best = cost;
+            best_k = k;
+            best_ax = ax;
+          }
         }
       }
     }
-    if (best_ax >= 0) {
-      if (best_ax != 2) sort_on(best_ax);  // (a total order: the same permutation as before)
-      for (uint32_t i = 0; i < n; i++) perm[lo + i] = keyed[i].rec;
+    // the chosen order's first best_k records go left; the other orders follow, stably
+    for (uint32_t i = 0; i < best_k; i++) left[ord[best_ax][lo + i]] = 1;
+    for (int ax = 0; ax < 3; ax++) {
+      if (ax == best_ax) continue;
+      uint32_t* o = ord[ax].data() + lo;
+      uint32_t l = 0, r = 0;
+      for (uint32_t i = 0; i < n; i++) {
+        if (left[o[i]])
+          o[l++] = o[i];
+        else
+          tmp[r++] = o[i];
+      }
+      std::copy(tmp.begin(), tmp.begin() + r, o + l);
     }
+    for (uint32_t i = 0; i < best_k; i++) left[ord[best_ax][lo + i]] = 0;
     return lo + best_k;
   }
   // orders the <= 16 records of a quad-level node into groups of four
@@ -635,8 +645,10 @@ inline std::vector<LbNode> build_leaf_sah(const fs_scene_desc* s, const LeafJob&
   int levels = 0;
   while (SahLeafBuilder::cap(levels) < n) levels++;
   levels = levels + 2 < FS2_LBVH_MAX_LEVELS - 1 ? levels + 2 : FS2_LBVH_MAX_LEVELS - 1;
-  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}};
+  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}, {}, {}};
+  b.presort();
   b.build(0, 0, n, levels);
+  perm = b.ord[0];
   if (nodes.size() >= 65536) return {};  // stack entries carry 16-bit node offsets
   for (uint32_t i = 0; i < n; i++) {
     uint32_t src = perm[i];

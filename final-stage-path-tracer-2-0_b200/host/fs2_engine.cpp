@@ -191,14 +191,28 @@ DisplayFrame::~DisplayFrame() {
     fs_host_unregister(f.mat_id.data());
   }
 }
-void DisplayFrame::Reset() {  // frame.cpp:43-51
-  FrameImpl& f = *impl_;
+// Reset() clears 43 bytes per pixel on the host (frame.cpp:43-51) that the next TraceScene
+// overwrites anyway (5 ms at 1080p, more than a sixth of an 8-GPU frame): the fill is deferred
+// until somebody looks at the buffers before they have been rewritten.
+static void zero_picture(FrameImpl& f) {
   std::fill(f.mean.begin(), f.mean.end(), 0.f);
-  std::fill(f.normal.begin(), f.normal.end(), 0.f);
-  std::fill(f.depth.begin(), f.depth.end(), 0.f);
   std::fill(f.count.begin(), f.count.end(), 0u);
   std::fill(f.rgb8.begin(), f.rgb8.end(), (uint8_t)0);
+}
+static void zero_guides(FrameImpl& f) {
+  std::fill(f.normal.begin(), f.normal.end(), 0.f);
+  std::fill(f.depth.begin(), f.depth.end(), 0.f);
   std::fill(f.mat_id.begin(), f.mat_id.end(), (uint64_t)0);
+}
+static void materialise(FrameImpl& f) {
+  if (!f.zero_pending) return;
+  f.zero_pending = false;
+  zero_picture(f);
+  zero_guides(f);
+}
+void DisplayFrame::Reset() {  // frame.cpp:43-51
+  FrameImpl& f = *impl_;
+  f.zero_pending = true;
   f.samples = 0;
   f.device_dirty = true;
   f.aux_stale = false;
@@ -209,6 +223,7 @@ void DisplayFrame::Reset() {  // frame.cpp:43-51
 void DisplayFrame::WritePixel(const vector3& pixel, uint32 x, uint32 y) {
   FrameImpl& f = *impl_;
   if (x >= f.width || y >= f.height) return;
+  materialise(f);
   const size_t i = (size_t)y * f.width + x;
   float* m = &f.mean[3 * i];
   const float n0 = (float)f.count[i];
@@ -232,22 +247,34 @@ void DisplayFrame::WritePixel(const TraceResult& result, uint32 x, uint32 y) {  
   f.depth[i] = result.depth;
   f.mat_id[i] = result.material_id;
 }
-uint8* DisplayFrame::GetDisplayBuffer() { return impl_->rgb8.data(); }
+uint8* DisplayFrame::GetDisplayBuffer() {
+  materialise(*impl_);
+  return impl_->rgb8.data();
+}
 uint32 DisplayFrame::GetWidth() { return impl_->width; }
 uint32 DisplayFrame::GetHeight() { return impl_->height; }
 float32 DisplayFrame::GetAspectRatio() { return (float32)impl_->width / impl_->height; }
 void DisplayFrame::SetFrameCount(uint32 count) { impl_->frame_count = count; }
-const float32* DisplayFrame::GetRenderTarget() { return impl_->mean.data(); }
-const uint32* DisplayFrame::GetCountBuffer() { return impl_->count.data(); }
+const float32* DisplayFrame::GetRenderTarget() {
+  materialise(*impl_);
+  return impl_->mean.data();
+}
+const uint32* DisplayFrame::GetCountBuffer() {
+  materialise(*impl_);
+  return impl_->count.data();
+}
 const float32* DisplayFrame::GetNormalBuffer() {
+  materialise(*impl_);
   fetch_aux(impl_.get());
   return impl_->normal.data();
 }
 const float32* DisplayFrame::GetDepthBuffer() {
+  materialise(*impl_);
   fetch_aux(impl_.get());
   return impl_->depth.data();
 }
 const uint64* DisplayFrame::GetMaterialIdBuffer() {
+  materialise(*impl_);
   fetch_aux(impl_.get());
   return impl_->mat_id.data();
 }
@@ -329,6 +356,7 @@ int TraceSamples(const Camera& view, Scene* scene, DisplayFrame* output, uint32 
   if (fs_film_read(st.ctx, f->mean.data(), f->count.data(), f->rgb8.data(), nullptr, nullptr, nullptr) != FS_OK)
     return fail("fs_film_read", st.ctx);
   f->aux_stale = true;
+  f->zero_pending = false;  // the picture was just rewritten, the guide planes come from the device
   return 0;
 }
 
@@ -405,6 +433,10 @@ bool LoadFilmCheckpoint(DisplayFrame* frame, const char* path) {
     }
     st.film_w = f->width;
     st.film_h = f->height;
+  }
+  if (f->zero_pending) {  // the picture is rewritten below; the guide planes stay cleared
+    zero_guides(*f);
+    f->zero_pending = false;
   }
   if (fs_film_load(st.ctx, sums.data()) != FS_OK ||
       fs_film_read(st.ctx, f->mean.data(), f->count.data(), f->rgb8.data(), nullptr, nullptr, nullptr) != FS_OK) {

@@ -57,6 +57,7 @@ struct FrameImpl {
   uint32_t samples = 0;  // samples accumulated since the last Reset()
   bool device_dirty = true;  // device film must be cleared before the next launch
   bool pinned = false;       // buffers are page-locked (fs_host_register)
+  bool zero_pending = false; // Reset() was called: the host buffers read as zero, the fill is deferred
   bool aux_stale = false;    // normal / depth / material-id planes are newer on the device
   bool host_written = false; // WritePixel changed the host buffers: upload before the next launch
 };

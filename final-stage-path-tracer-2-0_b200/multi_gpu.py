@@ -53,10 +53,13 @@ def film_tensor(ctx):
 
 
 def aux_tensors(ctx):
-    """torch views of the aux planes: float4 (normal, depth) and int32 material id per pixel."""
+    """torch views of the aux planes: float4 (normal, depth) and material id per pixel, both as
+    int32 words.  Under tile sharding every pixel's record lives on exactly one rank and is zero
+    elsewhere, so an integer sum gathers it with its bit pattern intact (a float sum would turn a
+    -0.0 normal component into +0.0)."""
     aux, mat, n = ctx.film_device_aux()
     dev = "cuda:%d" % ctx.device
-    return (torch.as_tensor(_DevicePtr(aux, 4 * n), device=dev),
+    return (torch.as_tensor(_DevicePtr(aux, 4 * n, "<i4"), device=dev),
             torch.as_tensor(_DevicePtr(mat, n, "<i4"), device=dev))
 
 
