@@ -311,6 +311,9 @@ def run_gpu(args, cfg, rank, world, local_rank):
     W, H, SPP = cfg["width"], cfg["height"], cfg["spp"]
 
     scene_file = scene_path(cfg["scene"], rank, world)
+    # mesh octrees are built on this rank's GPU (csrc/fs2_build.cuh: byte-identical to the host
+    # builder, tests/test_gpu_build.py); --host-build keeps the host builder
+    host.load_host_library().fs2h_set_gpu_build(-1 if args.host_build else local_rank)
     t0 = time.time()
     hs = host.HostScene(scene_file)
     if cfg["fog"]:
@@ -511,6 +514,7 @@ def run_gpu(args, cfg, rank, world, local_rank):
                            "baseline_config": args.config, "scene": cfg["what"],
                            "scene_bytes": hs.nbytes(), "host_load_build_s": round(load_s, 2),
                            "scene_upload_s": round(upload_s, 3),
+                           "mesh_octree_build": "host" if args.host_build else "device (k_bd_*)",
                            "sharding": sharding,
                            "l2": "flushed between steps (256 MiB write)", "seed": SEED,
                            "variant": args.variant, "untimed_ramp_steps": ramp_steps,
@@ -549,6 +553,7 @@ def main():
     ap.add_argument("--shard", default="auto", choices=["auto", "samples", "tiles"],
                     help="multi-GPU sharding: sample indices, interleaved tiles, or automatic")
     ap.add_argument("--skip-cpu", action="store_true", help="tuning runs: no cpu_baseline leg")
+    ap.add_argument("--host-build", action="store_true", help="build mesh octrees on the host, not the GPU")
     ap.add_argument("--variant", default="wavefront", choices=["phase", "wavefront", "lbvh_lane", "coop", "per_thread"],
                     help="leaf-scan variant of the trace kernel (A/B measurements)")
     args = ap.parse_args()

@@ -124,6 +124,41 @@ __device__ __forceinline__ Ray make_ray(V3 start, V3 stop) {
   return r;
 }
 
+// Read-only loads with an L1 policy.  FS2_CACHE_HINTS bit 0: triangle records (read once per
+// ray, 64 + 48 + 4 bytes each) do not allocate in L1; bit 1: tree nodes are evicted last.
+#ifndef FS2_CACHE_HINTS
+#define FS2_CACHE_HINTS 0
+#endif
+__device__ __forceinline__ float4 ldg_once(const float4* p) {
+#if FS2_CACHE_HINTS & 1
+  float4 v;
+  asm volatile("ld.global.nc.L1::no_allocate.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+#else
+  return __ldg(p);
+#endif
+}
+__device__ __forceinline__ uint32_t ldg_once(const uint32_t* p) {
+#if FS2_CACHE_HINTS & 1
+  uint32_t v;
+  asm volatile("ld.global.nc.L1::no_allocate.u32 %0, [%1];" : "=r"(v) : "l"(p));
+  return v;
+#else
+  return __ldg(p);
+#endif
+}
+__device__ __forceinline__ float4 ldg_keep(const float4* p) {
+#if FS2_CACHE_HINTS & 2
+  float4 v;
+  asm volatile("ld.global.nc.L1::evict_last.v4.f32 {%0,%1,%2,%3}, [%4];"
+               : "=f"(v.x), "=f"(v.y), "=f"(v.z), "=f"(v.w) : "l"(p));
+  return v;
+#else
+  return __ldg(p);
+#endif
+}
+
 // reference source/math/intersect.cpp:16-24 (inclusive on both sides)
 __device__ __forceinline__ bool point_in_box(V3 mn, V3 mx, V3 p) {
   return p.x >= mn.x && p.x <= mx.x && p.y >= mn.y && p.y <= mx.y && p.z >= mn.z && p.z <= mx.z;

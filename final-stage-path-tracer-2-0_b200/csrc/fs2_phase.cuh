@@ -581,8 +581,8 @@ template <bool STATS>
 __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray& r,
                                            const LbRay& q, const PhSmem& sm, Counters& c) {
   const float4* nd = S.lb_nodes + 8 * (size_t)w.lb_cur;
-  float4 lx = __ldg(nd), ly = __ldg(nd + 1), lz = __ldg(nd + 2);
-  float4 hx = __ldg(nd + 3), hy = __ldg(nd + 4), hz = __ldg(nd + 5);
+  float4 lx = ldg_keep(nd), ly = ldg_keep(nd + 1), lz = ldg_keep(nd + 2);
+  float4 hx = ldg_keep(nd + 3), hy = ldg_keep(nd + 4), hz = ldg_keep(nd + 5);
   uint4 meta = __ldg((const uint4*)(nd + 6));
   if (STATS) c.n_lbnode++;
   const V3 s = r.start;
@@ -639,6 +639,104 @@ __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray
     return;
   }
   ph_lb_pop(w, S, sm);
+}
+
+// Warp-cooperative form of ph_lb_node, called by the whole (converged) warp; `owners` = lanes in
+// PH_LB_NODE.  ncu on the per-lane form (profiles/r2_c_*): the four child box tests run at 9 of
+// 32 lanes, the sort / push code at 5.5, together 18 % of the kernel's instructions, and the six
+// float4 child planes set its register peak.  Here a node's four children go to four lanes (up to
+// 8 owners per pass): each lane loads one child's box (6 scalars), runs one lb_child, ranks itself
+// among its three neighbours by (entry parameter, child index) with three shuffles, and the lanes
+// of the far children write the owner's stack column in shared memory directly; the owner only
+// takes the nearest child (or the hit mask of a quad-level node) back.  The visiting order is
+// nearest first like the per-lane form's sorting network; exactness does not depend on it (the
+// walk returns the lexicographic minimum (t, leaf rank) of what it reaches, and culls with <=).
+template <bool STATS>
+__device__ __forceinline__ void ph_lb_node_coop(const DScene& S, PhLane& w, const Ray& r,
+                                                const LbRay& q, const PhSmem& sm, Counters& c,
+                                                unsigned owners, volatile uint8_t* slot_owner) {
+  const unsigned FULL = 0xFFFFFFFFu;
+  const int lane = threadIdx.x & 31;
+  const unsigned below = (1u << lane) - 1u;
+  const bool own = (owners >> lane) & 1u;
+  if (STATS && own) c.n_lbnode++;
+  const float my_lim = fminf(w.rec.param, 1.0f);
+  bool none = false;  // this owner's node had no child to continue with: pop
+  unsigned todo = owners;
+  while (todo) {
+    const uint32_t rank = (uint32_t)__popc(todo & below);
+    const bool served = ((todo >> lane) & 1u) && rank < 8u;
+    if (served) slot_owner[rank] = (uint8_t)lane;
+    __syncwarp();
+    const uint32_t n_served = min((uint32_t)__popc(todo), 8u);
+    const uint32_t slot = (uint32_t)lane >> 2, j = (uint32_t)lane & 3u;
+    const bool active = slot < n_served;
+    const int src = active ? (int)slot_owner[slot] : 0;
+    __syncwarp();
+    const uint32_t node = __shfl_sync(FULL, w.lb_cur, src);
+    const V3 s = v3(__shfl_sync(FULL, r.start.x, src), __shfl_sync(FULL, r.start.y, src),
+                    __shfl_sync(FULL, r.start.z, src));
+    LbRay qq;
+    qq.idx = __shfl_sync(FULL, q.idx, src);
+    qq.idy = __shfl_sync(FULL, q.idy, src);
+    qq.idz = __shfl_sync(FULL, q.idz, src);
+    const float lim = __shfl_sync(FULL, my_lim, src);
+    const uint32_t sp = (uint32_t)__shfl_sync(FULL, w.lb_sp, src);
+    const uint32_t root = __shfl_sync(FULL, w.lb_root, src);
+    float t = 3.0f;
+    uint4 meta = make_uint4(0u, 0u, 0u, 0u);
+    if (active) {
+      const float* nd = reinterpret_cast<const float*>(S.lb_nodes + 8 * (size_t)node);
+      meta = __ldg(reinterpret_cast<const uint4*>(nd + 24));
+      t = lb_child(__ldg(nd + j), __ldg(nd + 4 + j), __ldg(nd + 8 + j), __ldg(nd + 12 + j),
+                   __ldg(nd + 16 + j), __ldg(nd + 20 + j), s, qq, lim);
+    }
+    const bool hit = t < 3.0f;
+    const unsigned hit_b = __ballot_sync(FULL, hit);
+    const uint32_t hits4 = (hit_b >> (slot << 2)) & 15u;
+    // children in front of this one: smaller entry parameter, or the same and a lower index
+    uint32_t before = 0;
+#pragma unroll
+    for (uint32_t d = 1; d < 4; d++) {
+      const float ot = __shfl_xor_sync(FULL, t, d);
+      before += (ot < t || (ot == t && (j ^ d) < j)) ? 1u : 0u;
+    }
+    const unsigned first_b = __ballot_sync(FULL, hit && before == 0u);
+    const uint32_t nhit = (uint32_t)__popc(hits4);
+    if (active && hit && !meta.y && before >= 1u) {
+      // pending sibling: the farthest lowest on the stack, so the nearest pops first
+      const uint32_t pos = sp + (nhit - 1u - before);
+      if (pos < (uint32_t)FS2_PH_LB_STACK)
+        (sm.col + (src - lane))[sm.lslot((int)pos) * FS2_PH_THREADS] =
+            ((meta.x + j - root) << 16) | (__float_as_uint(t) >> 16);
+    }
+    // hand the node's verdict back to its owner (read from the slot's first lane)
+    const int from = served ? (int)(rank << 2) : 0;
+    const uint32_t jbest = (uint32_t)__ffs((int)((first_b >> (slot << 2)) & 15u));  // 1-based, 0 = none
+    const uint32_t packed = hits4 | (jbest << 4) | (meta.y ? 256u : 0u);
+    const uint32_t r_packed = __shfl_sync(FULL, packed, from);
+    const uint32_t r_x = __shfl_sync(FULL, meta.x, from), r_z = __shfl_sync(FULL, meta.z, from);
+    if (served) {
+      const uint32_t h4 = r_packed & 15u, jb = (r_packed >> 4) & 7u;
+      if (!h4) {
+        none = true;
+      } else if (r_packed & 256u) {
+        w.qbase = r_x;
+        w.qcount = r_z;
+        w.qmask = h4;
+        prefetch_l1(S.lb_plane + r_x + 4u * ((uint32_t)__ffs((int)h4) - 1u));
+        w.st = PH_LB_TRIS;
+      } else {
+        w.lb_cur = r_x + jb - 1u;  // stays in PH_LB_NODE
+        prefetch_l1(S.lb_nodes + 8 * (size_t)w.lb_cur);
+        const uint32_t nsp = (uint32_t)w.lb_sp + (uint32_t)__popc(h4) - 1u;
+        w.lb_sp = (int)(nsp < (uint32_t)FS2_PH_LB_STACK ? nsp : (uint32_t)FS2_PH_LB_STACK);
+      }
+    }
+    todo &= ~__ballot_sync(FULL, served);
+  }
+  __syncwarp();  // the stack columns written by other lanes are read by ph_lb_pop
+  if (none) ph_lb_pop(w, S, sm);
 }
 
 template <bool STATS>
@@ -710,13 +808,13 @@ __device__ __forceinline__ void ph_lb_tris_coop(const DScene& S, PhLane& w, cons
     uint32_t kord = 0xFFFFFFFFu;
     if (slot < n_served && j < no) {
       const uint32_t k = ko + j;
-      float4 pl = __ldg(S.lb_plane + k);
+      float4 pl = ldg_once(S.lb_plane + k);
       float ts = pl.x * d.x + pl.y * d.y + pl.z * d.z;
       if (!near_zero(ts)) {
         float ns = -(pl.x * s.x + pl.y * s.y + pl.z * s.z + pl.w);
         float t = ns / ts;
         if (t >= 0.0f && t <= 1.0f && (t < bt || (t == bt && found))) {
-          uint32_t ord = __ldg(S.lb_order + k);
+          uint32_t ord = ldg_once(S.lb_order + k);
           if (t < bt || ord < border) {
             if (STATS) c.n_bary++;
             float uu, vv;

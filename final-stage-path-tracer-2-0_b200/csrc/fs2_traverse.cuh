@@ -145,7 +145,7 @@ __device__ __forceinline__ bool ray_box(V3 mn, V3 mx, const Ray& r, float& param
 // 146-177; constants hoisted by include/fs2_pack.h with the same operations).
 __device__ __forceinline__ bool tri_inside(const float4* __restrict__ aux, V3 point, float& u,
                                            float& v) {
-  float4 a0 = __ldg(aux), a1 = __ldg(aux + 1), a2 = __ldg(aux + 2);
+  float4 a0 = ldg_once(aux), a1 = ldg_once(aux + 1), a2 = ldg_once(aux + 2);
   V3 vp = point - v3(a0.x, a0.y, a0.z);
   uint32_t drop = __float_as_uint(a0.w) >> 30;
   float vpa = (drop == 0u) ? vp.y : vp.x;
@@ -257,7 +257,7 @@ struct NodeRec {
 // carries the occupancy of its eight children in its top byte (node indices are < 2^24).
 #define FS2_NODE_INDEX_BITS 24
 __device__ __forceinline__ NodeRec load_node(const DScene& S, uint32_t i) {
-  float4 a = __ldg(S.nodes + 2 * (size_t)i), b = __ldg(S.nodes + 2 * (size_t)i + 1);
+  float4 a = ldg_keep(S.nodes + 2 * (size_t)i), b = ldg_keep(S.nodes + 2 * (size_t)i + 1);
   NodeRec n;
   n.mn = v3(a.x, a.y, a.z);
   n.mx = v3(b.x, b.y, b.z);

@@ -206,6 +206,14 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #ifndef FS2_WF_REPEAT_MIN_OBJ
 #define FS2_WF_REPEAT_MIN_OBJ 2
 #endif
+#ifndef FS2_WF_COOP_NODE
+#define FS2_WF_COOP_NODE 0  // 1: leaf-BVH nodes with the four child boxes on four lanes (ph_lb_node_coop).  Measured:
+                            // config 2 623 vs 723 Mpaths/s per lane, grid4m 467 vs 613 — masked-off lanes cost nothing,
+                            // the 12 shuffles, 3 ballots and two warp syncs of a pass cost more than the divergence
+#endif
+#ifndef FS2_WF_REPEAT_MIN_NODE
+#define FS2_WF_REPEAT_MIN_NODE 3
+#endif
 #ifndef FS2_WF_COOP_TRIS
 #define FS2_WF_COOP_TRIS 1  // triangle groups tested by 4 lanes each (ph_lb_tris_coop)
 #endif
@@ -296,7 +304,16 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
                   (ph_object<STATS, TREE>(S, w, ray, c)))
     }
     FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, (ph_enter<STATS, TREE>(S, w, ray, sm, c)))
+#if FS2_WF_COOP_NODE
+#pragma unroll 1
+    for (int rep_ = 0; rep_ < FS2_WF_REP_NODE; ++rep_) {
+      unsigned m_ = __ballot_sync(FULL, w.st == PH_LB_NODE);
+      if (!m_ || (rep_ && __popc(m_) < FS2_WF_REPEAT_MIN_NODE)) break;
+      ph_lb_node_coop<STATS>(S, w, ray, q, sm, c, m_, s_slot_owner[threadIdx.x >> 5]);
+    }
+#else
     FS2_PHASE_N(PH_LB_NODE, FS2_WF_REP_NODE, FS2_WF_REPEAT_MIN, ph_lb_node<STATS>(S, w, ray, q, sm, c))
+#endif
 #if FS2_WF_COOP_TRIS
 #pragma unroll 1
     for (int rep_ = 0; rep_ < FS2_WF_REP_TRIS; ++rep_) {
