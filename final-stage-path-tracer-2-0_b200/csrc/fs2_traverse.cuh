@@ -68,6 +68,9 @@ __device__ __forceinline__ Hit no_hit() {
   return h;
 }
 
+#ifndef FS2_CUBOID_REJECT
+#define FS2_CUBOID_REJECT 1  // bounding-sphere early out in front of the cuboid's six-plane loop
+#endif
 #define FS2_MESH_STACK 5
 #define FS2_SCENE_STACK 8
 
@@ -497,6 +500,25 @@ __device__ __forceinline__ bool primitive_trace(const DScene& S, uint32_t oi, ui
       return false;
     }
     case FS_OBJ_CUBOID: {  // object.cpp:126-165
+#if FS2_CUBOID_REJECT
+      {
+        // Conservative early out (ncu on the 303-object scene: the six-plane loop below ran at 2-4
+        // of 32 lanes and was 45 % of the kernel's instructions although one object in ten is a
+        // cuboid).  A face is only accepted at a point p = start + dir * t that passes the other
+        // four plane tests, i.e. within rounding (~1e-6 (|centre| + R)) of the solid itself, which
+        // lies inside the sphere around the centre of Object::GetBounds() through its corners.  A
+        // segment whose supporting line stays outside that sphere — radius^2 padded by 5 % plus
+        // 4e-6 (|start - c|^2 + |c|^2), which also covers the cancellation in oo a - b^2 — or that
+        // starts outside it pointing away cannot reach any face.
+        const float4 w7 = obj_word(S, oi, 7), w8 = obj_word(S, oi, 8);
+        const V3 bmn = v3(w7.z, w7.w, w8.x), bmx = v3(w8.y, w8.z, w8.w);
+        const V3 cen = (bmn + bmx) * 0.5f, hd = (bmx - bmn) * 0.5f;
+        const V3 o = r.start - cen;
+        const float oo = dot(o, o), a = dot(r.dir, r.dir), b = dot(o, r.dir);
+        const float lim = 1.05f * dot(hd, hd) + 4.0e-6f * (oo + dot(cen, cen));
+        if (oo > lim && (b >= 0.0f || oo * a - b * b > lim * a)) return false;
+      }
+#endif
       bool detected = false;
 #pragma unroll 1
       for (int i = 0; i < 6; i++) {

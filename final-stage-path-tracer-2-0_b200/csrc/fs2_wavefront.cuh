@@ -342,8 +342,11 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
 
 // FRESH: fill the pool (every thread starts a path).  Otherwise: finish the traced segment of
 // live path `idx`, then continue it, or replace it by the next path id.
+#ifndef FS2_WF_SHADE_MIN_BLOCKS
+#define FS2_WF_SHADE_MIN_BLOCKS 1
+#endif
 template <bool FRESH>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, FS2_WF_SHADE_MIN_BLOCKS)
 k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
            unsigned long long* __restrict__ stats) {
   const unsigned FULL = 0xFFFFFFFFu;

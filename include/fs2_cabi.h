@@ -123,7 +123,9 @@ typedef struct fs_object {
   uint32_t material; /* index into materials[] */
   uint32_t u[4];
   float f[24];
-  float bmin[3]; /* Object::GetBounds(), informational (tree build input) */
+  float bmin[3]; /* Object::GetBounds(): tree build input; for a cuboid it must contain the solid
+                    (its eight vertices) — the device skips the six-plane test for segments that
+                    stay outside the sphere through the box's corners */
   float bmax[3];
 } fs_object; /* 24 + 96 + 24 = 144 bytes */
 
