@@ -343,7 +343,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
 // FRESH: fill the pool (every thread starts a path).  Otherwise: finish the traced segment of
 // live path `idx`, then continue it, or replace it by the next path id.
 #ifndef FS2_WF_SHADE_MIN_BLOCKS
-#define FS2_WF_SHADE_MIN_BLOCKS 1
+#define FS2_WF_SHADE_MIN_BLOCKS 8  // measured (config 3 scene / config 2 / config 1, Mpaths/s): 84 regs 3219 / 715 / 4040, 6 CTAs 3402 / 721 / 4234, 7 CTAs 3459 / 720 / 4281, 8 CTAs (64 regs) 3512 / 717 / 4247
 #endif
 template <bool FRESH>
 __global__ void __launch_bounds__(128, FS2_WF_SHADE_MIN_BLOCKS)
@@ -380,10 +380,14 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
   }
   // Counter traffic is aggregated per CTA: with one atomic per warp on three shared addresses
   // the kernel was bound by same-address atomic latency (ncu r1_h: 82 % long-scoreboard stalls
-  // on the atomics and the shuffles that wait for them).
-  __shared__ uint32_t s_cnt[4][2];
+  // on the atomics and the shuffles that wait for them).  Barriers are the next cost (ncu r2_c:
+  // 20 % of the stall samples): the common case — no padding pixels — takes five of them.
+  __shared__ uint32_t s_cnt[4][2];   // regeneration round: requests per warp
+  __shared__ uint32_t s_cmp[4][2];   // compaction: continuing / fresh paths per warp
   __shared__ unsigned long long s_base64;
   __shared__ uint32_t s_base[2];
+  __shared__ uint32_t s_stat[3];
+  if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;  // (first used after the loop's first barrier)
   const int warp = threadIdx.x >> 5;
   const unsigned below = (1u << lane) - 1u;
   // ---- regeneration: the threads that need a path take consecutive ids
@@ -413,46 +417,44 @@ k_wf_shade(DScene S, CamBasis cam, Film film, TraceParams tp, WfBuffers B,
         }
       }
     }
-    __syncthreads();  // s_cnt / s_base64 are rewritten by the next round
+    // another round only when somebody drew a padding pixel (the barrier also orders the reads
+    // of s_cnt / s_base64 above before the next round rewrites them)
+    if (!__syncthreads_or(need ? 1 : 0)) break;
   }
   // ---- compaction: live threads write their state densely into the other array, bounce
-  // paths from the front, new camera paths from the back
+  // paths from the front, new camera paths from the back; statistics ride on the same barriers
   unsigned ms = __ballot_sync(FULL, alive && !fresh), mp = __ballot_sync(FULL, alive && fresh);
-  __syncthreads();
-  if (lane == 0) {
-    s_cnt[warp][0] = (uint32_t)__popc(ms);
-    s_cnt[warp][1] = (uint32_t)__popc(mp);
-  }
-  __syncthreads();
-  if (threadIdx.x < 2) {
-    uint32_t t = s_cnt[0][threadIdx.x] + s_cnt[1][threadIdx.x] + s_cnt[2][threadIdx.x] + s_cnt[3][threadIdx.x];
-    s_base[threadIdx.x] = t ? atomicAdd(B.counters + (threadIdx.x ? 7 : 1), t) : 0u;
-  }
-  __syncthreads();
-  if (alive) {
-    const int k = fresh ? 1 : 0;
-    uint32_t off = s_base[k] + (warp > 0 ? s_cnt[0][k] : 0u) + (warp > 1 ? s_cnt[1][k] : 0u) +
-                   (warp > 2 ? s_cnt[2][k] : 0u) + (uint32_t)__popc((fresh ? mp : ms) & below);
-    wf_store_path(B.state[cur ^ 1u], B.cap, fresh ? B.cap - 1u - off : off, ps, pixslot);
-  }
+  uint32_t f = 0, hv = 0, sh = 0;
   if (!FRESH) {
-    // statistics: one atomic per CTA and counter
-    __shared__ uint32_t s_stat[3];
-    if (threadIdx.x < 3) s_stat[threadIdx.x] = 0;
-    __syncthreads();
-    uint32_t f = __reduce_add_sync(FULL, finished), hv = __reduce_add_sync(FULL, have ? 1u : 0u),
-             sh = __reduce_add_sync(FULL, n_shade);
-    if (lane == 0) {
+    f = __reduce_add_sync(FULL, finished);
+    hv = __reduce_add_sync(FULL, have ? 1u : 0u);
+    sh = __reduce_add_sync(FULL, n_shade);
+  }
+  if (lane == 0) {
+    s_cmp[warp][0] = (uint32_t)__popc(ms);
+    s_cmp[warp][1] = (uint32_t)__popc(mp);
+    if (!FRESH) {
       atomicAdd(&s_stat[0], f);
       atomicAdd(&s_stat[1], hv);
       atomicAdd(&s_stat[2], sh);
     }
-    __syncthreads();
-    if (threadIdx.x == 0) {
-      atomicAdd(stats + ST_PATHS, (unsigned long long)s_stat[0]);
-      atomicAdd(stats + ST_SEGMENTS, (unsigned long long)s_stat[1]);
-      atomicAdd(stats + ST_SHADE, (unsigned long long)s_stat[2]);
-    }
+  }
+  __syncthreads();
+  if (threadIdx.x < 2) {
+    uint32_t t = s_cmp[0][threadIdx.x] + s_cmp[1][threadIdx.x] + s_cmp[2][threadIdx.x] + s_cmp[3][threadIdx.x];
+    s_base[threadIdx.x] = t ? atomicAdd(B.counters + (threadIdx.x ? 7 : 1), t) : 0u;
+  } else if (!FRESH && threadIdx.x == 32) {
+    // statistics: one atomic per CTA and counter
+    atomicAdd(stats + ST_PATHS, (unsigned long long)s_stat[0]);
+    atomicAdd(stats + ST_SEGMENTS, (unsigned long long)s_stat[1]);
+    atomicAdd(stats + ST_SHADE, (unsigned long long)s_stat[2]);
+  }
+  __syncthreads();
+  if (alive) {
+    const int k = fresh ? 1 : 0;
+    uint32_t off = s_base[k] + (warp > 0 ? s_cmp[0][k] : 0u) + (warp > 1 ? s_cmp[1][k] : 0u) +
+                   (warp > 2 ? s_cmp[2][k] : 0u) + (uint32_t)__popc((fresh ? mp : ms) & below);
+    wf_store_path(B.state[cur ^ 1u], B.cap, fresh ? B.cap - 1u - off : off, ps, pixslot);
   }
 }
 
