@@ -450,6 +450,16 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
     }
     if (!running) break;
   }
+  // The loop ends when every pipe has reported an empty wave.  Leaving it on the wave bound
+  // instead would mean paths were dropped (pixel counts below n_samples): report it, never
+  // return FS_OK over an incomplete film.
+  for (int p = 0; p < pipes; p++)
+    if (!done[p]) {
+      for (int q = 0; q < pipes; q++) cudaStreamSynchronize(streams[q]);
+      if (*(volatile uint32_t*)(ctx->wf_host_live + p) != 0u)
+        return fail(ctx, FS_E_CUDA, "fs_trace: pipe %d still had %u live paths after %llu waves", p,
+                    *(volatile uint32_t*)(ctx->wf_host_live + p), max_waves);
+    }
   for (int p = 1; p < pipes; p++) {
     CUDA_TRY(ctx, cudaEventRecord(ctx->wf_join[p], streams[p]));
     CUDA_TRY(ctx, cudaStreamWaitEvent(ctx->stream, ctx->wf_join[p], 0));

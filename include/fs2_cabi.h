@@ -195,7 +195,10 @@ typedef struct fs_camera {
 #define FS_TRACE_NO_DOF 2     /* ignore aperture_size                            */
 #define FS_TRACE_WAVEFRONT 4  /* the default, named (kept for callers that set it) */
 #define FS_TRACE_NO_RESOLVE 8 /* skip the mean/gamma resolve (multi-GPU: resolve after the reduce) */
-#define FS_TRACE_ASYNC 16     /* do not wait for the result: the film is complete in stream order */
+#define FS_TRACE_ASYNC 16     /* skip the final synchronisation: the film is complete in stream order.
+                                 (The default pipeline's host loop follows the waves through an event
+                                 ring, so the call still returns only when the last wave has been
+                                 enqueued; the megakernel variants return at once.) */
 #define FS_TRACE_PER_THREAD 32 /* megakernel; every thread scans its own mesh leaves linearly, in reference order */
 #define FS_TRACE_COOP 64       /* megakernel; linear leaf scans done by the whole warp, 32 triangles per step */
 #define FS_TRACE_LBVH_LANE 128 /* megakernel; per-leaf 4-wide BVH walked by free-running lanes (nested loops) */
