@@ -23,6 +23,9 @@ namespace fs2 {
 
 // Leaves with fewer triangles than this are scanned directly (one node, no tree).
 #define FS2_LBVH_MAX_LEVELS 7  // 4^(7+1) = 65 536 triangles per octree leaf
+#ifndef FS2_LBVH_SAH_SLACK
+#define FS2_LBVH_SAH_SLACK 2  // order 3: inner levels beyond the fewest that hold the leaf (room for uneven cuts)
+#endif
 #ifndef FS2_LBVH_SAH_STEP
 #define FS2_LBVH_SAH_STEP 1u  // order 3: cut positions are multiples of this many records
 #endif
@@ -644,7 +647,7 @@ inline std::vector<LbNode> build_leaf_sah(const fs_scene_desc* s, const LeafJob&
   // uneven cuts, never more than the stack allows
   int levels = 0;
   while (SahLeafBuilder::cap(levels) < n) levels++;
-  levels = levels + 2 < FS2_LBVH_MAX_LEVELS - 1 ? levels + 2 : FS2_LBVH_MAX_LEVELS - 1;
+  levels = levels + FS2_LBVH_SAH_SLACK < FS2_LBVH_MAX_LEVELS - 1 ? levels + FS2_LBVH_SAH_SLACK : FS2_LBVH_MAX_LEVELS - 1;
   SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}, {}, {}};
   b.presort();
   b.build(0, 0, n, levels);

@@ -37,6 +37,12 @@ namespace fs2 {
 
 #define FS2_WF_PLANES 6          // float4 planes of per-path state
 #define FS2_WF_CHUNK 128         // most ray indices a warp reserves per atomic
+#ifndef FS2_EXP_ITERS
+#define FS2_EXP_ITERS 0  // diagnostic: per-ray loop iteration statistics in the stats build
+#endif
+#ifndef FS2_WF_CHUNK_MIN
+#define FS2_WF_CHUNK_MIN 8       // fewest (a power of two): the end of a wave and sparse waves; 1080p @ 8 spp: 32 -> 26.16, 16 -> 25.90, 8 -> 25.83 ms
+#endif
 #define FS2_WF_MAX_PATHS (1u << 25)  // pool size bound (state: 2 x 96 B + 20 B per path = 7.1 GB); measured on
                                      // config 2 at r1_l: 4 M -> 492, 8 M -> 520, 16 M -> 537, 32 M -> 544, 64 M -> 543 Mpaths/s
 
@@ -255,7 +261,13 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   uint32_t chunk_next = 0, chunk_end = 0;
   bool exhausted = false;
   const uint32_t fetch_min = max(1u, tp.tune & 31u);
+#if FS2_EXP_ITERS
+  uint32_t iters = 0;  // diagnostic build: loop iterations of this lane's current ray
+#endif
   for (;;) {
+#if FS2_EXP_ITERS
+    iters++;
+#endif
     // ---- fetch: idle lanes take the next rays of the warp's reserved chunk
     unsigned idle = __ballot_sync(FULL, w.st == PH_IDLE);
     if (idle && ((uint32_t)__popc(idle) >= fetch_min || idle == FULL || exhausted)) {
@@ -266,7 +278,8 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
         if (lane == 0) {
           uint32_t seen = *(volatile uint32_t*)(B.counters + 2);
           uint32_t left = seen < n_in ? n_in - seen : 0u;
-          chunk = min((uint32_t)FS2_WF_CHUNK, max(32u, (left / (2u * n_warps)) & ~31u));
+          chunk = min((uint32_t)FS2_WF_CHUNK,
+                      max((uint32_t)FS2_WF_CHUNK_MIN, (left / (2u * n_warps)) & ~((uint32_t)FS2_WF_CHUNK_MIN - 1u)));
           b = atomicAdd(B.counters + 2, chunk);
         }
         b = __shfl_sync(FULL, b, 0);
@@ -285,6 +298,9 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
           idx = wf_phys(chunk_next + rank, n_sec, B.cap);
           ray = wf_load_ray(st, B.cap, idx);
           q = ph_segment_start<TREE>(S, w, ray);
+#if FS2_EXP_ITERS
+          iters = 0;
+#endif
         }
         chunk_next += min((uint32_t)__popc(idle), avail);
       } else if (exhausted && idle == FULL) {
@@ -326,11 +342,19 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
 #endif
     FS2_PHASE_N(PH_RETURN, FS2_WF_REP_RETURN, FS2_WF_REPEAT_MIN, (ph_return<STATS, TREE>(S, w, ray, sm, c)))
     if (w.st == PH_SHADE) {  // nearest hit of the segment is final
+#if FS2_EXP_ITERS
+      if (STATS) {  // the work counters are borrowed: (sum of iterations, rays) for depth 0 / 1 / >= 2
+        const uint32_t depth = (__float_as_uint(__ldcs(st + idx + 2 * (size_t)B.cap).y) >> 8) & 255u;
+        const int k = depth == 0u ? 0 : depth == 1u ? 1 : 2;
+        atomicAdd(stats + (k == 0 ? ST_NODE : k == 1 ? ST_BARY : ST_LBNODE), (unsigned long long)iters);
+        atomicAdd(stats + (k == 0 ? ST_TRI : k == 1 ? ST_PRIM : ST_TRITEST), 1ull);
+      }
+#endif
       wf_store_hit(B, idx, w.rec);
       w.st = PH_IDLE;
     }
   }
-  if (STATS) {
+  if (STATS && !FS2_EXP_ITERS) {
     warp_add(stats + ST_NODE, c.n_node);
     warp_add(stats + ST_TRI, c.n_tri);
     warp_add(stats + ST_BARY, c.n_bary);
