@@ -66,6 +66,12 @@ struct fs_ctx {
   cudaStream_t wf_stream = nullptr;            // == wf_streams[1]: "the pipeline has been set up"
   cudaEvent_t wf_fork = nullptr, wf_join[FS2_WF_PIPES] = {};
   int pipes = 2;  // FS2_PIPES: parts the pool is split into
+  // Sparse waves (the drain of a frame): a persistent k_wf_trace that fills every SM slot keeps the
+  // other pipe's k_wf_shade — and with it that pipe's next wave — waiting until its own rays are
+  // done, so the two pipes alternate instead of overlapping.  Below drain_live live paths the
+  // traversal grid takes drain_ctas CTAs per SM only.
+  int drain_ctas = 0;            // FS2_DRAIN_CTAS (0: always the full grid)
+  uint32_t drain_live = 2u << 20;  // FS2_DRAIN_LIVE (paths)
   int sm_count = 148;
   // stats
   unsigned long long* d_stats = nullptr;
@@ -442,7 +448,10 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
       k_wf_flip<<<1, 1, 0, streams[p]>>>(B[p].counters, B[p].host_live);
       CUDA_TRY(ctx, cudaEventRecord(ev, streams[p]));
       stamp(p, wave, "flip", live_bound[p]);
-      trace_kernel<<<persistent, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
+      int grid = persistent;
+      if (ctx->drain_ctas > 0 && ctx->drain_ctas < per_sm && pipes > 1 && live_bound[p] < ctx->drain_live)
+        grid = ctx->sm_count * ctx->drain_ctas;
+      trace_kernel<<<grid, FS2_PH_THREADS, smem, streams[p]>>>(ctx->ds, B[p], tp, ctx->d_stats);
       stamp(p, wave, "trace", live_bound[p]);
       k_wf_shade<false><<<shade_blocks, 128, 0, streams[p]>>>(ctx->ds, cb, film, tp, B[p], ctx->d_stats);
       stamp(p, wave, "shade", live_bound[p]);
@@ -671,6 +680,8 @@ int fs_create(fs_ctx** out, int device, int flags) {
   ctx->stats_build = (flags & 1) != 0;
   if (const char* e = getenv("FS2_TUNE")) ctx->tune = (uint32_t)strtoul(e, nullptr, 0);
   ctx->timeline = getenv("FS2_TIMELINE");
+  if (const char* e = getenv("FS2_DRAIN_CTAS")) ctx->drain_ctas = atoi(e);
+  if (const char* e = getenv("FS2_DRAIN_LIVE")) ctx->drain_live = (uint32_t)strtoul(e, nullptr, 0);
   if (const char* e = getenv("FS2_PIPES")) {
     int n = atoi(e);
     ctx->pipes = n < 1 ? 1 : n > FS2_WF_PIPES ? FS2_WF_PIPES : n;
