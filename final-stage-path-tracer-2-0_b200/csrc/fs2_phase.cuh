@@ -98,8 +98,17 @@ struct PhLane {
 #define PH_F_FAR 16u  // segment starts beyond DScene::lb_origin_limit: linear mesh-leaf scans
 
 // ---- shared-memory columns
+#ifndef FS2_WF_STAGE_TOP
+#define FS2_WF_STAGE_TOP 0  // experiment: root + first level of the first 8 objects' mesh trees in shared memory.
+                            // Measured: config 2 657 vs 720 Mpaths/s, grid4m 565 vs 612 — off
+#endif
+#define FS2_STAGE_OBJECTS 8
+#define FS2_STAGE_NODES 9   // a root and its eight children (numbered depth first: contiguous)
+
 struct PhSmem {
   uint32_t* col;  // &smem[threadIdx.x]
+  const float4* top = nullptr;         // [FS2_STAGE_OBJECTS][2 * FS2_STAGE_NODES] staged node words
+  const uint32_t* top_root = nullptr;  // [FS2_STAGE_OBJECTS] root node index, 0xFFFFFFFF = not staged
   __device__ __forceinline__ uint32_t& w(int slot) const { return col[slot * FS2_PH_THREADS]; }
   __device__ __forceinline__ float& f(int slot) const {
     return reinterpret_cast<float*>(col)[slot * FS2_PH_THREADS];
@@ -112,6 +121,30 @@ struct PhSmem {
     return FS2_PH_MESH_FRAMES * FS2_PH_FRAME_WORDS + sp;
   }
 };
+
+// Node record of a mesh-tree walk: from the staged copy when the node is a staged root or one of
+// its children, from global memory otherwise.
+__device__ __forceinline__ NodeRec ph_load_node(const DScene& S, const PhSmem& sm, uint32_t obj, bool mesh,
+                                                uint32_t i) {
+#if FS2_WF_STAGE_TOP
+  if (mesh && obj < FS2_STAGE_OBJECTS && sm.top) {  // (only k_wf_trace stages)
+    const uint32_t rel = i - sm.top_root[obj];
+    if (rel < FS2_STAGE_NODES) {
+      const float4 a = sm.top[obj * (2 * FS2_STAGE_NODES) + 2 * rel], b = sm.top[obj * (2 * FS2_STAGE_NODES) + 2 * rel + 1];
+      NodeRec n;
+      n.mn = v3(a.x, a.y, a.z);
+      n.mx = v3(b.x, b.y, b.z);
+      n.count = __float_as_uint(b.w);
+      const uint32_t f = __float_as_uint(a.w);
+      const bool internal = n.count == FS_NODE_INTERNAL;
+      n.first = internal ? (f & ((1u << FS2_NODE_INDEX_BITS) - 1u)) : f;
+      n.cmask = internal ? (f >> FS2_NODE_INDEX_BITS) : 0u;
+      return n;
+    }
+  }
+#endif
+  return load_node(S, i);
+}
 
 // frame words: 0 node | bits << 25 (bits: 0-2 child, 3-4 visits, 5 returned a hit, 6 origin
 // inside), 1..3 tx ty tz, 4 entry parameter
@@ -169,7 +202,7 @@ template <bool STATS, bool TREE = true>
 __device__ __forceinline__ void ph_enter(const DScene& S, PhLane& w, const Ray& r,
                                          const PhSmem& sm, Counters& c) {
   const bool mesh = !TREE || (w.flags & PH_F_MESH) != 0;  // without a scene tree only meshes walk
-  NodeRec n = load_node(S, w.cur);
+  NodeRec n = ph_load_node(S, sm, w.cur_obj, mesh, w.cur);
 #if FS2_PH_EARLY_ROOT
   // the leaf-BVH root of a mesh leaf, fetched beside the node instead of after its box test
   // (one memory round trip less per leaf visit; wasted for internal nodes and misses)
@@ -278,10 +311,10 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
   const uint32_t packed = sm.w(sm.fslot(mesh, f, 0));
   const uint32_t node = packed & ((1u << FS2_PH_NODE_BITS) - 1u);
   uint32_t bits = packed >> FS2_PH_NODE_BITS;
-  NodeRec pn = load_node(S, node);
+  NodeRec pn = ph_load_node(S, sm, w.cur_obj, mesh, node);
   if (ret) {
     bits |= 32u;
-    NodeRec ch = load_node(S, pn.first + (bits & 7u));
+    NodeRec ch = ph_load_node(S, sm, w.cur_obj, mesh, pn.first + (bits & 7u));
     if (point_in_box(ch.mn, ch.mx, r.start + r.dir * w.rec.param)) {
       // ret stays true; continue returning into the parent frame, or finish with the last one
       if (--sp == 0 && FS2_PH_FUSE_DONE) ph_tree_done<TREE>(S, w, mesh, true);

@@ -237,6 +237,36 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
   __shared__ uint8_t s_slot_owner[FS2_PH_THREADS / 32][8];
   PhSmem sm;
   sm.col = ph_smem + threadIdx.x;
+#if FS2_WF_STAGE_TOP
+  {
+    // experiment (north_star: "shared-memory or TMA staging of hot octree nodes"): the root and
+    // first level of the first eight objects' mesh trees, 288 contiguous bytes each
+    __shared__ float4 s_top[FS2_STAGE_OBJECTS * 2 * FS2_STAGE_NODES];
+    __shared__ uint32_t s_top_root[FS2_STAGE_OBJECTS];
+    if (threadIdx.x < FS2_STAGE_OBJECTS) {
+      uint32_t root = 0xFFFFFFFFu;
+      if (threadIdx.x < S.n_objects) {
+        const float4 w0 = obj_word(S, threadIdx.x, 0);
+        if (__float_as_uint(w0.x) == FS_OBJ_MESH) {
+          const uint32_t r = __float_as_uint(w0.z);
+          if (r != 0xFFFFFFFFu) {
+            const NodeRec n = load_node(S, r);
+            if (n.count == FS_NODE_INTERNAL && n.first == r + 1u) root = r;
+          }
+        }
+      }
+      s_top_root[threadIdx.x] = root;
+    }
+    __syncthreads();
+    for (uint32_t i = threadIdx.x; i < FS2_STAGE_OBJECTS * 2 * FS2_STAGE_NODES; i += FS2_PH_THREADS) {
+      const uint32_t r = s_top_root[i / (2 * FS2_STAGE_NODES)];
+      if (r != 0xFFFFFFFFu) s_top[i] = __ldg(S.nodes + 2 * (size_t)r + i % (2 * FS2_STAGE_NODES));
+    }
+    __syncthreads();
+    sm.top = s_top;
+    sm.top_root = s_top_root;
+  }
+#endif
   const unsigned FULL = 0xFFFFFFFFu;
   const int lane = threadIdx.x & 31;
   const uint32_t n_sec = B.counters[0];
