@@ -217,6 +217,9 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
                             // config 2 623 vs 723 Mpaths/s per lane, grid4m 467 vs 613 — masked-off lanes cost nothing,
                             // the 12 shuffles, 3 ballots and two warp syncs of a pass cost more than the divergence
 #endif
+#if FS2_WF_COOP_NODE && FS2_PH_LB_STACK < 18
+#error "ph_lb_node_coop has no overflow fallback: it needs the worst-case stack (FS2_PH_LB_STACK >= 18)"
+#endif
 #ifndef FS2_WF_REPEAT_MIN_NODE
 #define FS2_WF_REPEAT_MIN_NODE 3
 #endif

@@ -112,3 +112,33 @@ def test_cli_exr_output_equals_the_pfm(tmp_path):
     assert lib.fs2h_load_image(exr.encode(), C.byref(w), C.byref(h), buf.ctypes.data_as(C.c_void_p), buf.size) == 0
     assert (w.value, h.value) == (72, 40)
     assert np.array_equal(buf.reshape(40, 72, 3)[::-1], mean)
+
+
+def test_cli_fast_preview_equals_the_abi_with_fast_render_enabled(tmp_path, ctx):
+    """--fast sets Camera::fast_render_enabled (reference source/engine.cpp:68-70: paths stop after
+    their second segment with radiance 1, what the reference renders while the mouse is down): the
+    image equals fs_trace with that camera flag and the same seed, and differs from the full one.
+    (The flag itself is pinned path by path against the reference in tests/test_gpu_paths.py.)"""
+    from fs2_b200 import host
+    exe = build.build_cli()
+    scene = gen_scenes.generate(str(tmp_path), ["demo"])["demo"]
+    common = [exe, "-f", scene, "-w", "96", "-h", "64", "--spp", "6", "--seed", "21"]
+
+    def run(extra, name):
+        pfm = str(tmp_path / (name + ".pfm"))
+        r = subprocess.run(common + extra + ["--out", str(tmp_path / (name + ".ppm")), "--pfm", pfm],
+                           capture_output=True, text=True)
+        assert r.returncode == 0, r.stdout + r.stderr
+        return np.frombuffer(open(pfm, "rb").read()[len(b"PF\n96 64\n-1.0\n"):], np.float32).reshape(64, 96, 3)
+
+    fast, full = run(["--fast"], "fast"), run([], "full")
+    hs = host.HostScene(scene)
+    cam = hs.camera()
+    cam.fast_render_enabled = 1
+    ctx.upload(hs.desc())
+    ctx.resize(96, 64)
+    ctx.reset()
+    ctx.trace(cam, 6, seed=21)
+    want = ctx.read_film()["mean"].reshape(64, 96, 3)
+    assert np.allclose(fast, want, rtol=2e-5, atol=1e-6)
+    assert np.abs(fast - full).mean() > 1e-3
