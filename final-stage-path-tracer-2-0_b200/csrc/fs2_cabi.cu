@@ -65,6 +65,7 @@ struct fs_ctx {
   cudaStream_t wf_streams[FS2_WF_PIPES] = {};  // [0] unused (the context's stream), [p] pipe p
   cudaStream_t wf_stream = nullptr;            // == wf_streams[1]: "the pipeline has been set up"
   cudaEvent_t wf_fork = nullptr, wf_join[FS2_WF_PIPES] = {};
+  bool prims_only = false;  // the resident scene lists no mesh (k_wf_trace's batched object loop)
   int pipes = 2;  // FS2_PIPES: parts the pool is split into
   // Sparse waves (the drain of a frame): a persistent k_wf_trace that fills every SM slot keeps the
   // other pipe's k_wf_shade — and with it that pipe's next wave — waiting until its own rays are
@@ -415,9 +416,16 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
   const unsigned long long max_waves = 8ull * ((total + pool - 1) / pool) + 8ull;
   const unsigned smem = ph_smem_bytes(ctx->ds.scene_root >= 0);
   int per_sm = 0;
-  void (*trace_kernel)(DScene, WfBuffers, TraceParams, unsigned long long*) =
-      ctx->stats_build ? (ctx->ds.scene_root >= 0 ? k_wf_trace<true, true> : k_wf_trace<true, false>)
-                       : (ctx->ds.scene_root >= 0 ? k_wf_trace<false, true> : k_wf_trace<false, false>);
+  // specialisations: scene tree or not; without one, brute-force lists that hold no mesh are
+  // walked FS2_PH_OBJ_BATCH_PRIMS entries per step (fs2_phase.cuh ph_object)
+  void (*trace_kernel)(DScene, WfBuffers, TraceParams, unsigned long long*);
+  if (ctx->ds.scene_root >= 0)
+    trace_kernel = ctx->stats_build ? k_wf_trace<true, true> : k_wf_trace<false, true>;
+  else if (ctx->prims_only)
+    trace_kernel = ctx->stats_build ? k_wf_trace<true, false, FS2_PH_OBJ_BATCH_PRIMS>
+                                    : k_wf_trace<false, false, FS2_PH_OBJ_BATCH_PRIMS>;
+  else
+    trace_kernel = ctx->stats_build ? k_wf_trace<true, false> : k_wf_trace<false, false>;
   CUDA_TRY(ctx, cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, trace_kernel, FS2_PH_THREADS, smem));
   if (per_sm < 1) per_sm = 1;
   const int persistent = ctx->sm_count * per_sm;  // one resident generation of CTAs
@@ -608,6 +616,9 @@ int scene_upload_one(fs_ctx* ctx, const fs_scene_desc* s, const std::vector<floa
   d.texels = (const float*)ctx->texels.p;
   d.lut = (const float4*)ctx->lut.p;
   d.n_objects = s->n_objects;
+  ctx->prims_only = true;
+  for (uint32_t i = 0; i < s->n_objects; i++)
+    if (s->objects[i].type == FS_OBJ_MESH) ctx->prims_only = false;
   d.n_lut = s->n_lut;
   d.sky_material = s->sky_material;
   d.scene_root = s->scene_root;

@@ -32,12 +32,10 @@ namespace fs2 {
 #define FS2_PH_THREADS 128
 #define FS2_PH_MESH_FRAMES 4   // mesh trees: internal nodes at depth 0..3 (mesh.cpp:16)
 #define FS2_PH_SCENE_FRAMES 5  // scene trees: internal nodes at depth 0..4 (<= ~2 M objects)
-#ifndef FS2_PH_LB_STACK
 #define FS2_PH_LB_STACK 18     // 6 inner leaf-BVH levels x 3 pending siblings: the worst case of any tree the
-#endif                         // builder makes.  A walk that would need more falls back to the exact linear scan
-                               // (ph_lb_overflow; parity-tested with a 3-entry stack).  Measured with 10 entries
-                               // (15.4 KB per CTA, carve-out 132 KB, L1 124 instead of 88 KB): config 2 +0.7 %,
-                               // grid4m -3.2 % (its 10^4-record leaves overflow now and then) - kept at 18
+                               // builder makes (fs2_lbvh_build.h caps the inner levels).  Measured and dropped: a
+                               // 10-entry stack (L1 124 instead of 88 KB: config 2 +0.7 %) with an exact linear-scan
+                               // fallback on overflow - the fallback's call site alone cost config 2 10 % (spills)
 #define FS2_PH_FRAME_WORDS 5    // node | bits << 25, tx, ty, tz, entry parameter
 #define FS2_PH_NODE_BITS 25     // octree node indices below 2^25 (checked by fs_scene_upload)
 #define FS2_PH_SLOTS_NOTREE (FS2_PH_MESH_FRAMES * FS2_PH_FRAME_WORDS + FS2_PH_LB_STACK)
@@ -376,18 +374,21 @@ __device__ __forceinline__ void ph_return(const DScene& S, PhLane& w, const Ray&
 // ------------------------------------------------------------------ object iteration
 // One object of the brute-force list (scene.cpp:230-233) or of the current scene-tree leaf
 // (scene.cpp:84-99).  Primitives are tested on the spot, a mesh starts its octree walk.
-#ifndef FS2_PH_OBJ_BATCH
-#define FS2_PH_OBJ_BATCH 1  // brute-force list: objects looked at per step (until a mesh starts its walk);
-                            // measured on config 2 (fused tree ends, median-split leaf BVH): 1 -> 651, 4 -> 629 Mpaths/s
-#endif
-template <bool STATS, bool TREE = true>
+// Brute-force list entries per OBJ step (template parameter, chosen per scene by the host).  With
+// meshes in the list one entry per step is best (config 2: 1 -> 651, 4 -> 629 Mpaths/s: lanes
+// leave for their octree walks at different entries).  Without any, every lane of the warp sits in
+// PH_OBJ for the whole segment and the loop overhead per entry is what is left: 16 per step gives
+// config 3's scene 3 388 -> 3 713 and config 1's 4 077 -> 4 497 Mpaths/s.  (A run-time count costs
+// config 2 4 %: the loop's registers.)
+#define FS2_PH_OBJ_BATCH_PRIMS 16
+template <bool STATS, bool TREE = true, int BATCH = 1>
 __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray& r, Counters& c) {
   const bool tree = TREE && S.scene_root >= 0;
   if (!tree) {
     // a few list entries per step: primitives are tested on the spot, the end of the list is
     // noticed in the step that tested the last one
 #pragma unroll 1
-    for (int k = 0; k < FS2_PH_OBJ_BATCH; k++) {
+    for (int k = 0; k < BATCH; k++) {
       if (w.obj_i >= S.n_objects) {
         w.st = PH_SHADE;
         return;
@@ -615,47 +616,6 @@ __device__ __forceinline__ void ph_lb_pop(PhLane& w, const DScene& S, const PhSm
   ph_leaf_done(w);
 }
 
-// Rare: the rest of the current leaf by the linear scan over its (permuted) records, with the
-// leaf BVH's own acceptance rule — (t, leaf rank) below the running best — so whatever the walk
-// has found so far stays valid.  Out of line, by value (see mesh_leaf_cold).
-struct LbLinearResult {
-  float t, u, v;
-  uint32_t ord;
-  bool found;
-  Counters c;
-};
-template <bool STATS>
-__device__ __noinline__ LbLinearResult lb_linear_cold(DScene S, uint32_t first, uint32_t count, V3 s, V3 d,
-                                                      float bt, uint32_t border, bool found, float bu,
-                                                      float bv, Counters c) {
-  LbLinearResult o;
-  lb_test_tris<STATS>(S, first, count, s, d, bt, border, found, bu, bv, c);
-  o.t = bt;
-  o.u = bu;
-  o.v = bv;
-  o.ord = border;
-  o.found = found;
-  o.c = c;
-  return o;
-}
-template <bool STATS>
-__device__ __forceinline__ void ph_lb_overflow(const DScene& S, PhLane& w, const Ray& r, Counters& c) {
-  const NodeRec n = load_node(S, w.cur);  // the octree leaf being searched
-  LbLinearResult o = lb_linear_cold<STATS>(S, n.first, n.count, r.start, r.dir, w.rec.param, w.rec.prim,
-                                           (w.flags & PH_F_FOUND) != 0, w.rec.u, w.rec.v, c);
-  c = o.c;
-  if (o.found) {
-    w.rec.param = o.t;
-    w.rec.object = w.cur_obj;
-    w.rec.prim = o.ord;
-    w.rec.u = o.u;
-    w.rec.v = o.v;
-    w.flags |= PH_F_FOUND;
-  }
-  w.lb_sp = 0;
-  ph_leaf_done(w);
-}
-
 template <bool STATS>
 __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray& r,
                                            const LbRay& q, const PhSmem& sm, Counters& c) {
@@ -700,16 +660,6 @@ __device__ __forceinline__ void ph_lb_node(const DScene& S, PhLane& w, const Ray
   FS2_CSWAP(t1, c1, t3, c3)
   FS2_CSWAP(t1, c1, t2, c2)
 #undef FS2_CSWAP
-  {
-    // The stack holds FS2_PH_LB_STACK pending siblings (a walk needs 10 at most on every scene
-    // measured; the worst case of a tree is 3 per inner level).  A walk that would need more gives
-    // the leaf to the exact linear scan instead of dropping a sibling.
-    const int pushes = (t1 < 3.0f ? 1 : 0) + (t2 < 3.0f ? 1 : 0) + (t3 < 3.0f ? 1 : 0);
-    if (w.lb_sp + pushes > FS2_PH_LB_STACK) {
-      ph_lb_overflow<STATS>(S, w, r, c);
-      return;
-    }
-  }
   if (t3 < 3.0f && w.lb_sp < FS2_PH_LB_STACK) {
     sm.w(sm.lslot(w.lb_sp)) = ((c3 - w.lb_root) << 16) | (__float_as_uint(t3) >> 16);
     w.lb_sp++;

@@ -231,7 +231,7 @@ __global__ void k_wf_flip(uint32_t* counters, uint32_t* host_live) {
 #endif
 // TREE = false: the scene has no scene octree (< 182 objects), which lets the
 // compiler drop the scene-leaf bookkeeping (second hit record, leaf cursor) from the loop.
-template <bool STATS, bool TREE>
+template <bool STATS, bool TREE, int OBJB = 1>
 // (with a scene tree the per-lane stacks are 252 B: shared memory holds 7 CTAs per SM, so that
 // specialisation may use the registers of 7)
 __global__ void __launch_bounds__(FS2_PH_THREADS, TREE ? (FS2_WF_MIN_BLOCKS < 7 ? FS2_WF_MIN_BLOCKS : 7) : FS2_WF_MIN_BLOCKS)
@@ -350,7 +350,7 @@ k_wf_trace(DScene S, WfBuffers B, TraceParams tp, unsigned long long* __restrict
       }
     } else {
       FS2_PHASE_N(PH_OBJ, (TREE ? FS2_WF_REP_OBJ_TREE : FS2_WF_REP_OBJ), FS2_WF_REPEAT_MIN,
-                  (ph_object<STATS, TREE>(S, w, ray, c)))
+                  (ph_object<STATS, TREE, OBJB>(S, w, ray, c)))
     }
     FS2_PHASE_N(PH_ENTER, FS2_WF_REP_ENTER, FS2_WF_REPEAT_MIN, (ph_enter<STATS, TREE>(S, w, ray, sm, c)))
 #if FS2_WF_COOP_NODE
