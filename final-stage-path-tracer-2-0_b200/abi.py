@@ -63,6 +63,7 @@ class fs_scene_desc(C.Structure):
                 ("lut", C.c_void_p)]
 
 
+FS_TRACE_RAYS_STATIC_MAX = 32768  # most rays per fs_trace_rays_static call (include/fs2_cabi.h)
 # fs_ray_hit (fs_trace_rays)
 RAY_HIT_DT = np.dtype([("param", "<f4"), ("point", "<f4", 3), ("normal", "<f4", 3), ("uv", "<f4", 2),
                        ("object", "<u4"), ("face", "<u4"), ("material", "<u4"), ("is_internal", "<u4")])

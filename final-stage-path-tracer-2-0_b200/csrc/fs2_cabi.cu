@@ -13,6 +13,7 @@
 #include <stdlib.h>
 #include <string.h>
 
+#include <mutex>
 #include <string>
 #include <thread>
 #include <vector>
@@ -970,6 +971,69 @@ int fs_trace_rays(fs_ctx* ctx, const float* segments, int n_rays, fs_ray_hit* ou
   if ((rc = dev_alloc(ctx, &ctx->scratch, in_b + out_b + 64))) return rc;
   float* d_seg = (float*)ctx->scratch.p;
   fs_ray_hit* d_out = (fs_ray_hit*)((char*)ctx->scratch.p + ((in_b + 63) & ~(size_t)63));
+  CUDA_TRY(ctx, cudaMemcpyAsync(d_seg, segments, in_b, cudaMemcpyHostToDevice, ctx->stream));
+  k_probe_rays<<<(n_rays + FS2_LB_THREADS - 1) / FS2_LB_THREADS, FS2_LB_THREADS, 0, ctx->stream>>>(
+      ctx->ds, d_seg, n_rays, d_out);
+  ctx->launches++;
+  CUDA_TRY(ctx, cudaGetLastError());
+  CUDA_TRY(ctx, cudaMemcpyAsync(out, d_out, out_b, cudaMemcpyDeviceToHost, ctx->stream));
+  CUDA_TRY(ctx, cudaStreamSynchronize(ctx->stream));
+  return FS_OK;
+}
+
+// ---- fs_trace_rays_static: the same query with its scratch in the library image (no allocation).
+// Layout of the array: FS_TRACE_RAYS_STATIC_MAX segments (24 B each), then as many fs_ray_hit
+// records (52 B each); both parts start on a 256-byte boundary.
+#define FS2_STATIC_SEG_BYTES ((size_t)FS_TRACE_RAYS_STATIC_MAX * 24)
+#define FS2_STATIC_HIT_BYTES ((size_t)FS_TRACE_RAYS_STATIC_MAX * sizeof(fs_ray_hit))
+static_assert(FS2_STATIC_SEG_BYTES % 256 == 0, "the hit records must start on a 256-byte boundary");
+static __device__ __align__(256) unsigned char g_static_ray_scratch[FS2_STATIC_SEG_BYTES + FS2_STATIC_HIT_BYTES];
+
+namespace {
+// In host code `g_static_ray_scratch` is a host-side stand-in, not a device address: a kernel given
+// it faults (or, where the GPU can reach host memory, silently uses the wrong memory).  Every
+// device has its own copy of the array, so its address is looked up once per device, with that
+// device current, and kept here.
+#define FS2_STATIC_DEVICES 64
+std::mutex g_static_lock;
+void* g_static_ptr[FS2_STATIC_DEVICES] = {};
+
+int static_ray_scratch(fs_ctx* ctx, unsigned char** out) {
+  if (ctx->device < 0 || ctx->device >= FS2_STATIC_DEVICES)
+    return fail(ctx, FS_E_INVALID, "fs_trace_rays_static: device ordinal %d beyond %d", ctx->device,
+                FS2_STATIC_DEVICES - 1);
+  std::lock_guard<std::mutex> hold(g_static_lock);
+  if (!g_static_ptr[ctx->device]) {
+    int rc = set_device(ctx);  // the lookup answers for the current device
+    if (rc) return rc;
+    void* p = nullptr;
+    CUDA_TRY(ctx, cudaGetSymbolAddress(&p, g_static_ray_scratch));
+    if (!p) return fail(ctx, FS_E_CUDA, "fs_trace_rays_static: cudaGetSymbolAddress returned a null address");
+    g_static_ptr[ctx->device] = p;
+  }
+  *out = (unsigned char*)g_static_ptr[ctx->device];
+  return FS_OK;
+}
+}  // namespace
+
+int fs_trace_rays_static(fs_ctx* ctx, const float* segments, int n_rays, fs_ray_hit* out) {
+  if (!ctx || n_rays < 0 || (n_rays && (!segments || !out)))
+    return fail(ctx, FS_E_INVALID, "fs_trace_rays_static: bad argument");
+  if (n_rays > FS_TRACE_RAYS_STATIC_MAX)
+    return fail(ctx, FS_E_INVALID,
+                "fs_trace_rays_static: %d rays exceed the fixed scratch of FS_TRACE_RAYS_STATIC_MAX = %d "
+                "(split the batch or call fs_trace_rays)", n_rays, FS_TRACE_RAYS_STATIC_MAX);
+  if (!ctx->have_scene) return fail(ctx, FS_E_NOSCENE, "fs_trace_rays_static before fs_scene_upload");
+  if (!n_rays) return FS_OK;
+  int rc = set_device(ctx);
+  if (rc) return rc;
+  unsigned char* base = nullptr;
+  if ((rc = static_ray_scratch(ctx, &base))) return rc;
+  // Nothing in the array has to be cleared: the n_rays segments the kernel reads are overwritten
+  // here, and it writes every one of the n_rays records that are copied back.
+  float* d_seg = (float*)base;
+  fs_ray_hit* d_out = (fs_ray_hit*)(base + FS2_STATIC_SEG_BYTES);
+  const size_t in_b = (size_t)n_rays * 24, out_b = (size_t)n_rays * sizeof(fs_ray_hit);
   CUDA_TRY(ctx, cudaMemcpyAsync(d_seg, segments, in_b, cudaMemcpyHostToDevice, ctx->stream));
   k_probe_rays<<<(n_rays + FS2_LB_THREADS - 1) / FS2_LB_THREADS, FS2_LB_THREADS, 0, ctx->stream>>>(
       ctx->ds, d_seg, n_rays, d_out);

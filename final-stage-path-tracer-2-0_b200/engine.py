@@ -35,6 +35,7 @@ _SYMBOLS = {
     "fs_trace_range": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_int, C.c_int,
                                  C.c_float, C.c_float, C.POINTER(C.c_float)]),
     "fs_trace_rays": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
+    "fs_trace_rays_static": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "fs_sample_sky": (C.c_int, [C.c_void_p, C.c_void_p, C.c_int, C.c_void_p]),
     "fs_trace": (C.c_int, [C.c_void_p, C.POINTER(abi.fs_camera), C.c_uint32, C.c_uint32,
                            C.c_uint32, C.c_uint64, C.c_int]),
@@ -176,6 +177,15 @@ class Context:
                                                    np.asarray(stops, np.float32).reshape(-1, 3)], axis=1))
         out = np.zeros(len(seg), abi.RAY_HIT_DT)
         self._check(self.lib.fs_trace_rays(self.handle, _ptr(seg), len(seg), _ptr(out)))
+        return out
+
+    def trace_rays_static(self, starts, stops):
+        """fs_trace_rays_static: trace_rays without any device allocation (fixed scratch in the
+        library image, at most abi.FS_TRACE_RAYS_STATIC_MAX rays per call)."""
+        seg = np.ascontiguousarray(np.concatenate([np.asarray(starts, np.float32).reshape(-1, 3),
+                                                   np.asarray(stops, np.float32).reshape(-1, 3)], axis=1))
+        out = np.zeros(len(seg), abi.RAY_HIT_DT)
+        self._check(self.lib.fs_trace_rays_static(self.handle, _ptr(seg), len(seg), _ptr(out)))
         return out
 
     def sample_sky(self, views):

@@ -290,6 +290,23 @@ typedef struct fs_ray_hit {
  * Host pointers. */
 int fs_trace_rays(fs_ctx* ctx, const float* segments, int n_rays, fs_ray_hit* out);
 
+/* fs_trace_rays for callers that must not allocate device memory (code under CUDA graph capture,
+ * tight serving loops, harnesses that forbid cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same arguments and results as fs_trace_rays, bit for bit,
+ * but the staged segments and hit records live in a fixed array in device global memory that is
+ * part of the library image (FS_TRACE_RAYS_STATIC_MAX rays = 2 490 368 bytes, held by every GPU
+ * that loads the library until the process exits); the call makes no cudaMalloc / cudaFree and
+ * uses no allocating library routine.
+ *   - n_rays > FS_TRACE_RAYS_STATIC_MAX is refused with FS_E_INVALID and a message naming the limit
+ *     (split the batch, or use fs_trace_rays).
+ *   - Every call on a device shares that one array; it keeps the previous call's contents.  Nothing
+ *     in it has to start at zero: a call overwrites the n_rays segments it reads and the kernel
+ *     writes all n_rays records it returns.
+ *   - Calls that overlap on the GPU race (two contexts on one device, or two host threads): callers
+ *     serialise them.  The call itself is synchronous like fs_trace_rays. */
+#define FS_TRACE_RAYS_STATIC_MAX 32768
+int fs_trace_rays_static(fs_ctx* ctx, const float* segments, int n_rays, fs_ray_hit* out);
+
 /* Replaces Scene::SampleSky(depth, view) (reference source/scene.h:131, source/scene.cpp:157-162)
  * for n view directions (3 floats each); rgb gets 3 floats per query.  The reference's `depth`
  * argument does not reach LightMaterial::Sample's result and is not part of the call. */
