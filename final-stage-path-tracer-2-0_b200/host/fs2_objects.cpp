@@ -348,13 +348,15 @@ MeshObject::MeshObject(const std::string& filename, bool invert_normals,
       impl_->verts.push_back(v);
     }
   }
+  impl_->normals.reserve(obj.normals.size() / 3);
   for (size_t i = 0; i + 2 < obj.normals.size(); i += 3) {
     Vec3 n = normalize(Vec3(obj.normals[i], obj.normals[i + 1], obj.normals[i + 2]));
     if (invert_normals) n = n * -1.0;
     impl_->normals.push_back(n);
   }
-  impl_->texcoords = obj.texcoords;
+  impl_->texcoords.swap(obj.texcoords);
   // reversed winding (mesh.cpp:250-260)
+  impl_->faces.reserve(obj.corners.size() / 9);
   for (size_t j = 0; j + 8 < obj.corners.size(); j += 9) {
     MeshFaceRec f;
     for (int k = 0; k < 3; k++) {

@@ -95,3 +95,71 @@ def test_large_mesh_against_live_reference(tmp_path):
     ref = normalise(abi.FlatScene.load(blob))
     mine = normalise(host.HostScene(path).to_flat())
     assert mine.diff(ref) == []
+
+
+def test_obj_parser_threads_do_not_change_the_result(tmp_path):
+    """The .obj reader cuts the file into stretches parsed by several host threads
+    (host/fs2_assets.cpp load_obj).  The flattened scene must not depend on the thread count:
+    a deliberately awkward file — relative (negative) indices that reach back across stretch
+    boundaries, polygons, v / v/vt / v//vn / v/vt/vn corners, CRLF line ends, comments, blank
+    and junk lines — flattens to the same bytes with 1, 3 and all threads."""
+    rng = np.random.default_rng(4)
+    lines = ["# awkward obj", "o thing", ""]
+    nv = nt = nn = 0
+    for block in range(160):
+        k = int(rng.integers(40, 90))
+        base = nv
+        for _ in range(k):
+            p = rng.normal(size=3) * 6.0 + np.array([0.0, 8.0, 0.0])
+            lines.append("v %.7g %.7g %.7g" % tuple(p) + ("\r" if block % 3 == 0 else ""))
+            nv += 1
+        for _ in range(k // 2):
+            lines.append("vt %.5f %.5f" % tuple(rng.random(2)))
+            nt += 1
+        for _ in range(k // 3):
+            lines.append("vn %.5f %.5f %.5f" % tuple(rng.normal(size=3)))
+            nn += 1
+        lines.append("# block %d" % block)
+        lines.append("   ")
+        lines.append("g part%d" % block)
+        for _ in range(k):
+            m = int(rng.integers(3, 6))  # triangles, quads, pentagons (fan-triangulated)
+            style = int(rng.integers(0, 5))
+            corners = []
+            for _ in range(m):
+                if style == 4:  # relative indices: -1 is the newest element; some reach far back
+                    back = int(rng.integers(1, min(nv, 4000) + 1))
+                    corners.append("%d/%d/%d" % (-back, -int(rng.integers(1, nt + 1)), -int(rng.integers(1, nn + 1))))
+                    continue
+                v = int(rng.integers(base, nv)) + 1
+                t = int(rng.integers(0, nt)) + 1
+                n = int(rng.integers(0, nn)) + 1
+                corners.append(["%d" % v, "%d/%d" % (v, t), "%d//%d" % (v, n), "%d/%d/%d" % (v, t, n)][style])
+            lines.append("f " + " ".join(corners) + ("\r" if block % 5 == 0 else ""))
+    obj = tmp_path / "awkward.obj"
+    obj.write_text("\n".join(lines) + "\n")
+    assert obj.stat().st_size > 6 * 65536  # enough text for several stretches
+    scene = tmp_path / "awkward.scene"
+    scene.write_text("material m\n{\n    color 0.8 0.7 0.6\n}\nmaterial sky\n{\n    emission 1 1 1\n}\n"
+                     "sky\n{\n    material sky\n}\n"
+                     "mesh\n{\n    file %s\n    material m\n    translation 0.5 0 0\n    scale 1 1 1\n}\n" % obj)
+    blobs = []
+    saved = os.environ.get("FS2_HOST_THREADS")
+    try:
+        for threads in ("1", "3", None):
+            if threads is None:
+                os.environ.pop("FS2_HOST_THREADS", None)
+            else:
+                os.environ["FS2_HOST_THREADS"] = threads
+            hs = host.HostScene(str(scene))
+            blob = str(tmp_path / ("t%s.fs2" % (threads or "all")))
+            hs.save_blob(blob)
+            assert hs.desc().n_faces > 20000
+            hs.close()
+            blobs.append(open(blob, "rb").read())
+    finally:
+        if saved is None:
+            os.environ.pop("FS2_HOST_THREADS", None)
+        else:
+            os.environ["FS2_HOST_THREADS"] = saved
+    assert blobs[0] == blobs[1] == blobs[2]
