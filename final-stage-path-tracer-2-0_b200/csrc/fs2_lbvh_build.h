@@ -466,23 +466,47 @@ struct SahLeafBuilder {
   std::vector<uint32_t> tmp;
   std::vector<uint8_t> left;
   std::vector<double> rarea;
+  std::vector<Box3> gathered;
 
+  // The records in the three centre orders, ties by record index.  Leaves hold up to 65 536
+  // records: a stable least-significant-digit radix sort over the order-preserving integer image
+  // of the key (-0 folded onto +0, as the float comparison sees them) gives the same permutation
+  // as a comparison sort by (key, record) in a third of the time.
   void presort() {
     const uint32_t n = (uint32_t)perm.size();
-    struct Keyed {
-      float key;
-      uint32_t rec;
-    };
-    std::vector<Keyed> keyed(n);
+    std::vector<uint32_t> key(n), a(n), b(n);
+    uint32_t count[2048];
     for (int ax = 0; ax < 3; ax++) {
-      for (uint32_t i = 0; i < n; i++) keyed[i] = Keyed{cen[3 * (size_t)i + ax], i};
-      std::sort(keyed.begin(), keyed.end(),
-                [](const Keyed& a, const Keyed& b) { return a.key < b.key || (a.key == b.key && a.rec < b.rec); });
-      ord[ax].resize(n);
-      for (uint32_t i = 0; i < n; i++) ord[ax][i] = keyed[i].rec;
+      for (uint32_t i = 0; i < n; i++) {
+        const float f = cen[3 * (size_t)i + ax] + 0.0f;  // -0.0f + 0.0f = +0.0f
+        uint32_t u;
+        memcpy(&u, &f, 4);
+        key[i] = (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+        a[i] = i;
+      }
+      if (n < 1024) {  // (three 2 048-bucket histograms cost more than the sort of a small leaf)
+        std::sort(a.begin(), a.end(), [&](uint32_t x, uint32_t y) { return key[x] < key[y] || (key[x] == key[y] && x < y); });
+      } else {
+        const int shift[3] = {0, 11, 22}, bits[3] = {11, 11, 10};
+        for (int pass = 0; pass < 3; pass++) {
+          const uint32_t mask = (1u << bits[pass]) - 1u;
+          memset(count, 0, sizeof(uint32_t) << bits[pass]);
+          for (uint32_t i = 0; i < n; i++) count[(key[a[i]] >> shift[pass]) & mask]++;
+          uint32_t sum = 0;
+          for (uint32_t d = 0; d <= mask; d++) {
+            const uint32_t c = count[d];
+            count[d] = sum;
+            sum += c;
+          }
+          for (uint32_t i = 0; i < n; i++) b[count[(key[a[i]] >> shift[pass]) & mask]++] = a[i];
+          a.swap(b);
+        }
+      }
+      ord[ax] = a;
     }
     left.assign(n, 0);
     tmp.resize(n);
+    gathered.resize(n);
   }
   static double area(const Box3& b) {
     double x = (double)b.hi[0] - b.lo[0], y = (double)b.hi[1] - b.lo[1], z = (double)b.hi[2] - b.lo[2];
@@ -521,16 +545,19 @@ struct SahLeafBuilder {
       double best = INFINITY;
       rarea.resize(n + 1);
       for (int ax = 0; ax < 3; ax++) {
+        // one gather of the boxes in this order, then both passes run over contiguous memory
         const uint32_t* o = ord[ax].data() + lo;
+        Box3* g = gathered.data();
+        for (uint32_t i = 0; i < n; i++) g[i] = boxes[o[i]];
         Box3 b;
         b.reset();
-        for (uint32_t i = n; i-- > 0;) {
-          b.add(boxes[o[i]]);
+        for (uint32_t i = n; i-- > kmin;) {  // rarea[k] is read for k >= kmin only
+          b.add(g[i]);
           rarea[i] = area(b);
         }
         b.reset();
         for (uint32_t k = 1; k <= kmax; k++) {
-          b.add(boxes[o[k - 1]]);
+          b.add(g[k - 1]);
           if (k < kmin || (step > 1 && k % step)) continue;
           double cost = area(b) * ((k + 3) / 4) + rarea[k] * ((n - k + 3) / 4);
           if (cost < best) {
@@ -648,7 +675,7 @@ inline std::vector<LbNode> build_leaf_sah(const fs_scene_desc* s, const LeafJob&
   int levels = 0;
   while (SahLeafBuilder::cap(levels) < n) levels++;
   levels = levels + FS2_LBVH_SAH_SLACK < FS2_LBVH_MAX_LEVELS - 1 ? levels + FS2_LBVH_SAH_SLACK : FS2_LBVH_MAX_LEVELS - 1;
-  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}, {}, {}};
+  SahLeafBuilder b{boxes, cen, perm, nodes, first, {}, {}, {}, {}, {}};
   b.presort();
   b.build(0, 0, n, levels);
   perm = b.ord[0];
