@@ -60,6 +60,9 @@ static inline unsigned ph_smem_bytes(bool scene_tree) {
 #ifndef FS2_PH_EARLY_ROOT
 #define FS2_PH_EARLY_ROOT 1  // measured: config 2 709 -> 723, grid4m 606 -> 614 Mpaths/s
 #endif
+#ifndef FS2_PH_SPHERE_BATCH
+#define FS2_PH_SPHERE_BATCH 1  // consecutive sphere references of a scene-tree leaf tested per OBJ step
+#endif
 #ifndef FS2_PH_SPHERE_FAST
 #define FS2_PH_SPHERE_FAST 1  // scene-tree leaves test spheres from DScene::sref_sphere
 #endif
@@ -417,26 +420,35 @@ __device__ __forceinline__ void ph_object(const DScene& S, PhLane& w, const Ray&
     w.st = PH_RETURN;
     return;
   }
-  const uint32_t k = w.sleaf_first + w.sleaf_i;
+  uint32_t k = w.sleaf_first + w.sleaf_i;
   w.sleaf_i++;
 #if FS2_PH_SPHERE_FAST
   {
     // spheres (most of what a many-object scene lists) are tested from the 16-byte copy of their
-    // centre and radius that sits beside the reference: one load, no dependent chain
-    const float4 sp = __ldg(S.sref_sphere + k);
+    // centre and radius that sits beside the reference: one load, no dependent chain.  A step takes
+    // a run of up to FS2_PH_SPHERE_BATCH consecutive sphere references (same order, same tests as
+    // one per step: the leaf-local record is updated in leaf order).
+    float4 sp = __ldg(S.sref_sphere + k);
     if (sp.w == sp.w) {
-      if (STATS) c.n_prim++;
-      float t;
-      if (sphere_test(v3(sp.x, sp.y, sp.z), sp.w, r, t) && t < w.rec.param) {
-        w.rec.param = t;
-        w.rec.object = __ldg(S.scene_refs + k);
-        w.rec.prim = 0xFFFFFFFFu;
-        if (w.rec.param < w.glob.param) {
-          w.glob = w.rec;
-          w.flags |= PH_F_SIMPROVED;
+#pragma unroll 1
+      for (int b = 0;;) {
+        if (STATS) c.n_prim++;
+        float t;
+        if (sphere_test(v3(sp.x, sp.y, sp.z), sp.w, r, t) && t < w.rec.param) {
+          w.rec.param = t;
+          w.rec.object = __ldg(S.scene_refs + k);
+          w.rec.prim = 0xFFFFFFFFu;
+          if (w.rec.param < w.glob.param) {
+            w.glob = w.rec;
+            w.flags |= PH_F_SIMPROVED;
+          }
         }
+        if (++b >= FS2_PH_SPHERE_BATCH || w.sleaf_i >= w.sleaf_count) return;
+        sp = __ldg(S.sref_sphere + k + 1);
+        if (!(sp.w == sp.w)) return;  // the next reference is not a sphere: its own step
+        k++;
+        w.sleaf_i++;
       }
-      return;
     }
   }
 #endif
