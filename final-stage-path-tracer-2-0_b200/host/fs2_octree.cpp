@@ -207,31 +207,31 @@ uint32_t build_mesh_tree(const std::vector<Vec3>& verts, std::vector<MeshFaceRec
   Box root;
   for (const Vec3& v : verts) root.add(v);
   std::vector<uint32_t> all(faces.size());
-  for (uint32_t i = 0; i < faces.size(); i++) {
+  parallel_for(faces.size(), threads, [&](size_t i) {
     MeshFaceRec& f = faces[i];
     if (f.plane.x == 0 && f.plane.y == 0 && f.plane.z == 0 && f.plane.w == 0) {
       Vec3 p0 = verts[f.v[0]], p1 = verts[f.v[1]], p2 = verts[f.v[2]];
       f.plane = plane_from(face_normal(p0, p1, p2), p0);
     }
-    all[i] = i;
-  }
+    all[i] = (uint32_t)i;
+  });
   uint32_t root_index = (uint32_t)out->nodes.size();
   if (gpu_build_device() >= 0) {
     // same tree, built by the CUDA library (csrc/fs2_build.cuh); byte-identical output
     std::vector<float> vbuf(3 * verts.size()), pbuf(4 * faces.size());
     std::vector<uint32_t> ibuf(3 * faces.size());
-    for (size_t i = 0; i < verts.size(); i++) {
+    parallel_for(verts.size(), threads, [&](size_t i) {
       vbuf[3 * i] = verts[i].x;
       vbuf[3 * i + 1] = verts[i].y;
       vbuf[3 * i + 2] = verts[i].z;
-    }
-    for (size_t i = 0; i < faces.size(); i++) {
+    });
+    parallel_for(faces.size(), threads, [&](size_t i) {
       for (int k = 0; k < 3; k++) ibuf[3 * i + k] = faces[i].v[k];
       pbuf[4 * i] = faces[i].plane.x;
       pbuf[4 * i + 1] = faces[i].plane.y;
       pbuf[4 * i + 2] = faces[i].plane.z;
       pbuf[4 * i + 3] = faces[i].plane.w;
-    }
+    });
     fs_mesh_tree t;
     int rc = fs_mesh_tree_build(gpu_build_device(), vbuf.data(), (uint32_t)verts.size(), ibuf.data(),
                                 pbuf.data(), (uint32_t)faces.size(), face_base, root_index,

@@ -2,6 +2,7 @@
 #ifndef FS2_OCTREE_H_
 #define FS2_OCTREE_H_
 
+#include <thread>
 #include <vector>
 
 #include "fs2_cabi.h"
@@ -31,6 +32,24 @@ struct FlatArrays {
   int32_t scene_root = -1;
   uint32_t sky = 0;
 };
+
+// body(i) for every i in [0, n), split over `threads` host threads in contiguous slices; the calls
+// must be independent of each other (every loop it is used for writes element i only).
+template <class Body>
+inline void parallel_for(size_t n, unsigned threads, Body body) {
+  if (threads > 32) threads = 32;
+  if (threads <= 1 || n < 65536) {
+    for (size_t i = 0; i < n; i++) body(i);
+    return;
+  }
+  std::vector<std::thread> pool;
+  for (unsigned t = 0; t < threads; t++)
+    pool.emplace_back([=]() {
+      const size_t lo = n / threads * t, hi = t + 1 == threads ? n : n / threads * (t + 1);
+      for (size_t i = lo; i < hi; i++) body(i);
+    });
+  for (std::thread& t : pool) t.join();
+}
 
 // Device the mesh octrees are built on (-1: on the host), and the device time spent there.
 int& gpu_build_device();

@@ -304,7 +304,9 @@ const fs_scene_desc* Scene::Flatten() {
       r.u[1] = face_base;
       r.u[2] = (oi->normals.size() ? 1u : 0u) | (oi->texcoords.size() ? 2u : 0u);
       r.u[3] = (uint32_t)oi->faces.size();
-      for (const MeshFaceRec& f : oi->faces) {
+      F.faces.resize((size_t)face_base + oi->faces.size());
+      parallel_for(oi->faces.size(), threads, [&](size_t i) {
+        const MeshFaceRec& f = oi->faces[i];
         fs_face_attr fa;
         memset(&fa, 0, sizeof fa);
         for (int k = 0; k < 3; k++) {
@@ -314,8 +316,8 @@ const fs_scene_desc* Scene::Flatten() {
             fa.uv[k][1] = oi->texcoords[2 * (size_t)f.t[k] + 1];
           }
         }
-        F.faces.push_back(fa);
-      }
+        F.faces[(size_t)face_base + i] = fa;
+      });
       r.u[0] = oi->mesh_loaded ? build_mesh_tree(oi->verts, oi->faces, face_base, &F, threads)
                                : 0xFFFFFFFFu;
     }
