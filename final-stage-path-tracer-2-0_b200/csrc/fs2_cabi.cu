@@ -333,22 +333,39 @@ int launch_wavefront_waves(fs_ctx* ctx, const CamBasis& cb, const Film& film, co
   unsigned long long pool = FS2_WF_MAX_PATHS;
   if (ctx->tune >> 8) pool = (unsigned long long)(ctx->tune >> 8) << 10;  // FS2_TUNE bits 8..
   if (pool > total) pool = total;
+  bool grow = false;
+  unsigned long long fit = FS2_WF_MAX_PATHS;
   if (!(ctx->tune >> 8) && (size_t)pool * 212 > ctx->wf_planes.bytes + ctx->wf_hit.bytes) {
     // the buffers have to grow: never take more than an eighth of what is free for the path
     // state.  Only then — cudaMemGetInfo costs milliseconds when several processes share the
     // driver, which showed as 35 -> 40 ms per frame at 8 GPUs when it ran on every call.
+    grow = true;
     size_t free_b = 0, total_b = 0;
     if (cudaMemGetInfo(&free_b, &total_b) == cudaSuccess) {
-      unsigned long long fit = (free_b / 8) / 212;
+      fit = (free_b / 8) / 212;
       if (fit < (1u << 20)) fit = 1u << 20;
       if (pool > fit) pool = fit;
     }
   }
   int pipes = (ctx->tune & 32u) || pool < (1u << 18) ? 1 : ctx->pipes;  // FS2_TUNE bit 5: one pipe
   const uint32_t cap = (uint32_t)(((pool + pipes - 1) / pipes + 127u) & ~127ull);
+  // Paths the buffers are sized for.  When they have to grow, the allocation (not the pool in use)
+  // is rounded up to a power of two within the same bounds: a context whose jobs get larger step
+  // by step reallocates a handful of times, not at every step.  (A reallocation frees and
+  // allocates gigabytes; in a multi-device context with peer mappings that is ~100 ms, seen as
+  // outliers in the resolution x spp sweep at 4 and 8 GPUs — even for a growth from 33.2 M to
+  // 33.5 M paths.)
+  size_t alloc_paths = (size_t)cap * pipes;
+  if (grow) {
+    size_t p2 = 1;
+    while (p2 < alloc_paths) p2 <<= 1;
+    const size_t bound = (size_t)(fit < FS2_WF_MAX_PATHS ? fit : FS2_WF_MAX_PATHS);
+    if (p2 > bound) p2 = bound;
+    if (p2 > alloc_paths) alloc_paths = p2;
+  }
   int rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_planes, (size_t)cap * pipes * FS2_WF_PLANES * 16 * 2))) return rc;
-  if ((rc = dev_alloc(ctx, &ctx->wf_hit, (size_t)cap * pipes * 20))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_planes, alloc_paths * FS2_WF_PLANES * 16 * 2))) return rc;
+  if ((rc = dev_alloc(ctx, &ctx->wf_hit, alloc_paths * 20))) return rc;
   if ((rc = dev_alloc(ctx, &ctx->wf_counters, 64 * (FS2_WF_PIPES + 1)))) return rc;
   if (!ctx->wf_host_live) {
     CUDA_TRY(ctx, cudaHostAlloc((void**)&ctx->wf_host_live, 64, cudaHostAllocMapped));
